@@ -1,0 +1,207 @@
+"""DAG -> straight-line C / CUDA C printer.
+
+The north star asks for a code generator that "takes the MTK-generated RHS,
+mass matrix and Jacobian of the index-reduced system and emits straight-line
+CUDA C compiled for sm_100a".  This module is that printer.  The same printer
+emits plain C (used only by tests to check generated code on the CPU).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+from .dag import (Graph, CONST, INPUT, ADD, SUB, MUL, DIV, NEG, SIN, COS, SQRT,
+                  ATAN2, ABS, MIN, MAX, SELGE, INTERP)
+
+
+def _lit(v: float) -> str:
+    if v == int(v) and abs(v) < 1e15:
+        return f"{int(v)}.0"
+    return repr(float(v))
+
+
+class Printer:
+    """Prints the nodes needed for a set of outputs as `const double xN = ...;`."""
+
+    def __init__(self, g: Graph, input_fmt: Dict[str, str], interp_fmt: str =
+                 "mb_interp_{kind}{deriv}(tb, {table}, {t})"):
+        self.g = g
+        self.input_fmt = input_fmt
+        self.interp_fmt = interp_fmt
+
+    def ref(self, n: int) -> str:
+        g = self.g
+        o = g.op[n]
+        if o == CONST:
+            v = g.val[n]
+            return _lit(v) if v >= 0 else f"({_lit(v)})"
+        if o == INPUT:
+            kind, idx = g.payload[n]
+            return self.input_fmt[kind].format(i=idx)
+        if o == NEG:
+            return f"(-{self.ref(g.a[n])})"
+        return f"x{n}"
+
+    def body(self, outs: Sequence[int], indent: str = "  ") -> List[str]:
+        g = self.g
+        lines: List[str] = []
+        r = self.ref
+        for n in g.reachable(outs):
+            o = g.op[n]
+            if o in (CONST, INPUT, NEG):
+                continue
+            a, b, c = g.a[n], g.b[n], g.c[n]
+            if o in (ADD, SUB, MUL, DIV):
+                e = f"{r(a)} {'+-*/'[o - ADD]} {r(b)}"
+            elif o == SIN:
+                e = f"sin({r(a)})"
+            elif o == COS:
+                e = f"cos({r(a)})"
+            elif o == SQRT:
+                e = f"sqrt({r(a)})"
+            elif o == ABS:
+                e = f"fabs({r(a)})"
+            elif o == ATAN2:
+                e = f"atan2({r(a)}, {r(b)})"
+            elif o == MIN:
+                e = f"fmin({r(a)}, {r(b)})"
+            elif o == MAX:
+                e = f"fmax({r(a)}, {r(b)})"
+            elif o == SELGE:
+                e = f"(({r(a)} >= 0.0) ? {r(b)} : {r(c)})"
+            elif o == INTERP:
+                kind, table, deriv = g.payload[n]
+                e = self.interp_fmt.format(kind=kind, deriv=deriv, table=table, t=r(a))
+            else:
+                raise NotImplementedError(o)
+            lines.append(f"{indent}const double x{n} = {e};")
+        return lines
+
+    def function(self, signature: str, assigns: Sequence[Tuple[str, int]],
+                 indent: str = "  ") -> str:
+        """`assigns` = [(lhs C expression, node)], written after all temporaries."""
+        outs = [n for _, n in assigns]
+        lines = [signature + " {"]
+        lines += self.body(outs, indent)
+        for lhs, n in assigns:
+            lines.append(f"{indent}{lhs} = {self.ref(n)};")
+        lines.append("}")
+        return "\n".join(lines)
+
+
+# ---------------------------------------------------------------------------
+# codegen-time sparse LU (static diagonal pivoting, Markowitz order)
+# ---------------------------------------------------------------------------
+
+def sparse_lu(g: Graph, W: Dict[Tuple[int, int], int], n: int):
+    """Symbolic LU of the sparse matrix W (dict (i,j)->node) with diagonal pivots
+    chosen in Markowitz (min fill) order at code-generation time.
+
+    Returns (order, invd, L, U): pivot order; invd[k] node of 1/pivot;
+    L[k] = [(i, node)] multipliers of rows eliminated with pivot k;
+    U[k] = [(j, node)] off-diagonal entries of pivot row k (remaining columns).
+    W is consumed.
+    """
+    rows: Dict[int, Dict[int, int]] = {i: {} for i in range(n)}
+    cols: Dict[int, set] = {j: set() for j in range(n)}
+    for (i, j), v in W.items():
+        if v == g.zero:
+            continue
+        rows[i][j] = v
+        cols[j].add(i)
+    remaining = set(range(n))
+    order: List[int] = []
+    invd: Dict[int, int] = {}
+    L: Dict[int, List[Tuple[int, int]]] = {}
+    U: Dict[int, List[Tuple[int, int]]] = {}
+    while remaining:
+        best, bestcost = None, None
+        for k in sorted(remaining):
+            if k not in rows[k]:
+                continue
+            rc = sum(1 for j in rows[k] if j in remaining) - 1
+            cc = sum(1 for i in cols[k] if i in remaining) - 1
+            cost = rc * cc
+            if bestcost is None or cost < bestcost:
+                best, bestcost = k, cost
+        if best is None:
+            raise ValueError("structurally zero diagonal: static pivoting impossible")
+        k = best
+        remaining.discard(k)
+        order.append(k)
+        d = rows[k][k]
+        inv = g.div(g.one, d)
+        invd[k] = inv
+        urow = [(j, v) for j, v in sorted(rows[k].items()) if j in remaining]
+        U[k] = urow
+        lk: List[Tuple[int, int]] = []
+        for i in sorted(cols[k]):
+            if i not in remaining:
+                continue
+            l = g.mul(rows[i][k], inv)
+            if l == g.zero:
+                continue
+            lk.append((i, l))
+            ri = rows[i]
+            for j, v in urow:
+                upd = g.mul(l, v)
+                if j in ri:
+                    ri[j] = g.sub(ri[j], upd)
+                else:
+                    ri[j] = g.neg(upd)
+                    cols[j].add(i)
+        L[k] = lk
+    return order, invd, L, U
+
+
+def lu_solve(g: Graph, order, invd, L, U, b: Sequence[int]) -> List[int]:
+    """x = W^-1 b using factors from `sparse_lu` (all node ids)."""
+    y = list(b)
+    for k in order:
+        yk = y[k]
+        if yk == g.zero:
+            continue
+        for i, l in L[k]:
+            y[i] = g.sub(y[i], g.mul(l, yk))
+    x = list(y)
+    for k in reversed(order):
+        acc = y[k]
+        for j, v in U[k]:
+            acc = g.sub(acc, g.mul(v, x[j]))
+        x[k] = g.mul(acc, invd[k])
+    return x
+
+
+def ldl_solve_factory(g: Graph, M: List[List[int]]):
+    """Straight-line LDL^T of a small dense SPD matrix (node ids); returns a
+    function rhs(list of nodes) -> solution nodes.  Used for the linear
+    subsystems MTK inlines into the RHS (reference: src/Multibody.jl:159-166,
+    `inline_linear_sccs=true`), e.g. the joint-space mass matrix."""
+    n = len(M)
+    Lm = [[g.zero] * n for _ in range(n)]
+    Dinv = [g.zero] * n
+    Dd = [g.zero] * n
+    for j in range(n):
+        d = M[j][j]
+        for k in range(j):
+            d = g.sub(d, g.mul(g.mul(Lm[j][k], Lm[j][k]), Dd[k]))
+        Dd[j] = d
+        Dinv[j] = g.div(g.one, d)
+        for i in range(j + 1, n):
+            s = M[i][j]
+            for k in range(j):
+                s = g.sub(s, g.mul(g.mul(Lm[i][k], Lm[j][k]), Dd[k]))
+            Lm[i][j] = g.mul(s, Dinv[j])
+
+    def solve(b: Sequence[int]) -> List[int]:
+        y = list(b)
+        for i in range(n):
+            for k in range(i):
+                y[i] = g.sub(y[i], g.mul(Lm[i][k], y[k]))
+        z = [g.mul(y[i], Dinv[i]) for i in range(n)]
+        x = list(z)
+        for i in reversed(range(n)):
+            for k in range(i + 1, n):
+                x[i] = g.sub(x[i], g.mul(Lm[k][i], x[k]))
+        return x
+
+    return solve
