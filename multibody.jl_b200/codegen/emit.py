@@ -89,17 +89,20 @@ class Printer:
 
 
 # ---------------------------------------------------------------------------
-# codegen-time sparse LU (static diagonal pivoting, Markowitz order)
+# codegen-time sparse LU (pivot sequence fixed at code-generation time)
 # ---------------------------------------------------------------------------
 
-def sparse_lu(g: Graph, W: Dict[Tuple[int, int], int], n: int):
-    """Symbolic LU of the sparse matrix W (dict (i,j)->node) with diagonal pivots
-    chosen in Markowitz (min fill) order at code-generation time.
+def sparse_lu(g: Graph, W: Dict[Tuple[int, int], int], n: int, pivots=None):
+    """Symbolic LU of the sparse matrix W (dict (i,j)->node).
 
-    Returns (order, invd, L, U): pivot order; invd[k] node of 1/pivot;
-    L[k] = [(i, node)] multipliers of rows eliminated with pivot k;
-    U[k] = [(j, node)] off-diagonal entries of pivot row k (remaining columns).
-    W is consumed.
+    `pivots` is a sequence of (row, col) chosen at code-generation time (see
+    `choose_pivots_numeric`); when None, diagonal pivots in Markowitz (min
+    fill) order are used.
+
+    Returns (order, invd, L, U), all indexed by elimination step s:
+    order[s] = (prow, pcol); invd[s] node of 1/pivot; L[s] = [(i, node)]
+    multipliers of the rows eliminated with that pivot; U[s] = [(j, node)]
+    remaining entries of the pivot row.  W is consumed.
     """
     rows: Dict[int, Dict[int, int]] = {i: {} for i in range(n)}
     cols: Dict[int, set] = {j: set() for j in range(n)}
@@ -108,36 +111,42 @@ def sparse_lu(g: Graph, W: Dict[Tuple[int, int], int], n: int):
             continue
         rows[i][j] = v
         cols[j].add(i)
-    remaining = set(range(n))
-    order: List[int] = []
+    rrem = set(range(n))
+    crem = set(range(n))
+    order: List[Tuple[int, int]] = []
     invd: Dict[int, int] = {}
     L: Dict[int, List[Tuple[int, int]]] = {}
     U: Dict[int, List[Tuple[int, int]]] = {}
-    while remaining:
-        best, bestcost = None, None
-        for k in sorted(remaining):
-            if k not in rows[k]:
-                continue
-            rc = sum(1 for j in rows[k] if j in remaining) - 1
-            cc = sum(1 for i in cols[k] if i in remaining) - 1
-            cost = rc * cc
-            if bestcost is None or cost < bestcost:
-                best, bestcost = k, cost
-        if best is None:
-            raise ValueError("structurally zero diagonal: static pivoting impossible")
-        k = best
-        remaining.discard(k)
-        order.append(k)
-        d = rows[k][k]
-        inv = g.div(g.one, d)
-        invd[k] = inv
-        urow = [(j, v) for j, v in sorted(rows[k].items()) if j in remaining]
-        U[k] = urow
+    for step in range(n):
+        if pivots is not None:
+            pr, pc = pivots[step]
+            if pc not in rows[pr]:
+                raise ValueError(f"pivot ({pr},{pc}) is structurally zero")
+        else:
+            best, bestcost = None, None
+            for k in sorted(rrem):
+                if k not in rows[k] or k not in crem:
+                    continue
+                rc = sum(1 for j in rows[k] if j in crem) - 1
+                cc = sum(1 for i in cols[k] if i in rrem) - 1
+                cost = rc * cc
+                if bestcost is None or cost < bestcost:
+                    best, bestcost = k, cost
+            if best is None:
+                raise ValueError("structurally zero diagonal: static diagonal pivoting impossible")
+            pr = pc = best
+        rrem.discard(pr)
+        crem.discard(pc)
+        order.append((pr, pc))
+        inv = g.div(g.one, rows[pr][pc])
+        invd[step] = inv
+        urow = [(j, v) for j, v in sorted(rows[pr].items()) if j in crem]
+        U[step] = urow
         lk: List[Tuple[int, int]] = []
-        for i in sorted(cols[k]):
-            if i not in remaining:
+        for i in sorted(cols[pc]):
+            if i not in rrem or pc not in rows[i]:
                 continue
-            l = g.mul(rows[i][k], inv)
+            l = g.mul(rows[i][pc], inv)
             if l == g.zero:
                 continue
             lk.append((i, l))
@@ -149,26 +158,66 @@ def sparse_lu(g: Graph, W: Dict[Tuple[int, int], int], n: int):
                 else:
                     ri[j] = g.neg(upd)
                     cols[j].add(i)
-        L[k] = lk
+        L[step] = lk
     return order, invd, L, U
 
 
 def lu_solve(g: Graph, order, invd, L, U, b: Sequence[int]) -> List[int]:
     """x = W^-1 b using factors from `sparse_lu` (all node ids)."""
     y = list(b)
-    for k in order:
-        yk = y[k]
+    for s, (pr, pc) in enumerate(order):
+        yk = y[pr]
         if yk == g.zero:
             continue
-        for i, l in L[k]:
+        for i, l in L[s]:
             y[i] = g.sub(y[i], g.mul(l, yk))
-    x = list(y)
-    for k in reversed(order):
-        acc = y[k]
-        for j, v in U[k]:
+    x = [g.zero] * len(order)
+    for s in reversed(range(len(order))):
+        pr, pc = order[s]
+        acc = y[pr]
+        for j, v in U[s]:
             acc = g.sub(acc, g.mul(v, x[j]))
-        x[k] = g.mul(acc, invd[k])
+        x[pc] = g.mul(acc, invd[s])
     return x
+
+
+def choose_pivots_numeric(Wnum, thresh: float = 0.1):
+    """Pivot sequence for `sparse_lu` from a numeric sample of W (dense ndarray,
+    structural zeros exactly 0): Markowitz cost with threshold partial pivoting
+    (|a_ij| >= thresh * max|a_.j| in its column), fill-in tracked on the sample."""
+    import numpy as np
+    A = np.array(Wnum, dtype=float)
+    n = A.shape[0]
+    nzmask = A != 0.0
+    rrem = list(range(n)); crem = list(range(n))
+    seq = []
+    for _ in range(n):
+        best = None
+        for j in crem:
+            colmax = max(abs(A[i, j]) for i in rrem)
+            if colmax == 0.0:
+                continue
+            cc = sum(1 for i in rrem if nzmask[i, j]) - 1
+            for i in rrem:
+                if not nzmask[i, j] or abs(A[i, j]) < thresh * colmax:
+                    continue
+                rc = sum(1 for jj in crem if nzmask[i, jj]) - 1
+                key = (rc * cc, -abs(A[i, j]) / colmax, i != j, i, j)
+                if best is None or key < best[0]:
+                    best = (key, i, j)
+        if best is None:
+            raise ValueError("numerically singular sample matrix")
+        _, pr, pc = best
+        seq.append((pr, pc))
+        rrem.remove(pr); crem.remove(pc)
+        for i in rrem:
+            if nzmask[i, pc]:
+                l = A[i, pc] / A[pr, pc]
+                for j in crem:
+                    if nzmask[pr, j]:
+                        A[i, j] -= l * A[pr, j]
+                        nzmask[i, j] = True
+    return seq
 
 
 def ldl_solve_factory(g: Graph, M: List[List[int]]):

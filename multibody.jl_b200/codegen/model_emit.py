@@ -1,0 +1,172 @@
+"""ReducedSystem -> one self-contained C / CUDA C model header.
+
+North star (1): "a new codegen backend that takes the MTK-generated RHS, mass
+matrix and Jacobian of the index-reduced system ... and emits straight-line
+CUDA C compiled for sm_100a".  The reduced system is the `ReducedSystem`
+built by `mechanics/` (stand-in for `mtkcompile`, reference
+src/Multibody.jl:184); this module prints, per model `X`:
+
+  mbm_X_rhs(u,p,t,tb,du)          du = f(u,p,t)          (prob.f, src/Multibody.jl:69)
+  mbm_X_jac(u,p,t,tb,Jnz)         analytic sparse df/du, fixed pattern (oracle, tests)
+  mbm_X_dT(u,p,t,tb,dT)           df/dt
+  mbm_X_factor(u,p,t,tb,c,LU)     W = c*M - J (c = 1/(gamma*h)) built and LU-factored
+                                  in one straight-line pass, pivot sequence fixed at
+                                  code-generation time
+  mbm_X_solve(LU,b)               in-place W^-1 b with those factors
+
+plus sizes, the sparsity pattern, the mass-matrix diagonal and the algorithmic
+flop counts of each function (BASELINE.md section 4 cost table).
+
+The includer defines MB_FN (e.g. `static inline` or `__device__ __noinline__`)
+and provides `mb_interp_{cubic,linear}{0,1,2,3}(tb, table, t)`.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .dag import Graph, Ex, CONST
+from .emit import Printer, sparse_lu, lu_solve
+
+
+class ModelCode:
+    """Everything the emitter derived from a ReducedSystem (also used by tests)."""
+
+    def __init__(self, sys, pivots: Optional[Sequence[Tuple[int, int]]] = None):
+        self.sys = sys
+        g: Graph = sys.g
+        n = sys.n
+        self.n, self.m = n, sys.m
+        u_nodes = sys.u_nodes()
+        t_node = sys.t_node()
+        # --- analytic Jacobian (sparse) and time derivative -------------------
+        J = g.diff(sys.rhs, u_nodes)
+        self.jac_entries: List[Tuple[int, int, int]] = []      # (row, col, node)
+        for i in range(n):
+            for j in sorted(J[i]):
+                self.jac_entries.append((i, j, J[i][j]))
+        dT = g.diff(sys.rhs, [t_node])
+        self.dT_nodes = [dT[i].get(0, g.zero) for i in range(n)]
+        # --- fused W build + LU ------------------------------------------------
+        c = g.input("c", 0)
+        W: Dict[Tuple[int, int], int] = {}
+        for i, j, node in self.jac_entries:
+            W[(i, j)] = g.neg(node)
+        for i in range(n):
+            if sys.mass_diag[i]:
+                W[(i, i)] = g.add(W.get((i, i), g.zero), c)
+        self.W_pattern = sorted(W)
+        order, invd, L, U = sparse_lu(g, W, n, pivots=pivots)
+        # LU storage: for each elimination step, [1/pivot, U row entries..., L column entries...]
+        self.lu_nodes: List[int] = []
+        self.lu_slots: Dict[Tuple[str, int, int], int] = {}
+
+        def slot(kind, k, idx, node):
+            self.lu_slots[(kind, k, idx)] = len(self.lu_nodes)
+            self.lu_nodes.append(node)
+        for step, (pr, pc) in enumerate(order):
+            slot("d", step, 0, invd[step])
+            for j, v in U[step]:
+                slot("u", step, j, v)
+            for i, l in L[step]:
+                slot("l", step, i, l)
+        self.order, self.L, self.U, self.invd = order, L, U, invd
+        # --- solve graph (separate, tiny) ------------------------------------------
+        sg = Graph()
+        self.solve_graph = sg
+
+        def lu_in(kind, k, idx):
+            s = self.lu_slots[(kind, k, idx)]
+            node = self.lu_nodes[s]
+            if g.op[node] == CONST:             # structural constants need no load
+                return sg.const(g.val[node])
+            return sg.input("lu", s)
+        sL = {k: [(i, lu_in("l", k, i)) for i, _ in L[k]] for k in range(n)}
+        sU = {k: [(j, lu_in("u", k, j)) for j, _ in U[k]] for k in range(n)}
+        sD = {k: lu_in("d", k, 0) for k in range(n)}
+        b = [sg.input("b", i) for i in range(n)]
+        self.solve_out = lu_solve(sg, order, sD, sL, sU, b)
+        # --- flop counts -----------------------------------------------------------
+        self.F_rhs = g.flops(sys.rhs)
+        self.F_jac = g.flops([e[2] for e in self.jac_entries])
+        self.F_dT = g.flops(self.dT_nodes)
+        self.F_factor = g.flops(self.lu_nodes)
+        self.F_solve = sg.flops(self.solve_out)
+        self.F_lu_only = self.F_factor - self.F_jac   # structured LU alone (approx.; CSE shared)
+
+    @property
+    def nnz(self) -> int:
+        return len(self.jac_entries)
+
+    @property
+    def nlu(self) -> int:
+        return len(self.lu_nodes)
+
+
+def _carray(ctype: str, name: str, vals, per_line: int = 16) -> str:
+    vals = list(vals)
+    if not vals:
+        return f"static const {ctype} {name}[1] = {{0}};"
+    rows = []
+    for k in range(0, len(vals), per_line):
+        rows.append("  " + ", ".join(str(v) for v in vals[k:k + per_line]))
+    return f"static const {ctype} {name}[{len(vals)}] = {{\n" + ",\n".join(rows) + "\n};"
+
+
+def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
+    code = code or ModelCode(sys)
+    g = sys.g
+    X = sys.name
+    n, m = sys.n, sys.m
+    fmt = {"u": "u[{i}]", "p": "p[{i}]", "t": "t", "c": "c"}
+    pr = Printer(g, fmt, interp_fmt="mb_interp_{kind}{deriv}(tb, {table}, {t})")
+    args = "const double* MB_RESTRICT u, const double* MB_RESTRICT p, double t, const double* MB_RESTRICT tb"
+    out: List[str] = []
+    out.append(f"// GENERATED by multibody.jl_b200/codegen/model_emit.py -- do not edit.")
+    out.append(f"// model '{X}': n={n} states, m={m} parameters, nnz(J)={code.nnz}, LU slots={code.nlu}")
+    out.append(f"// algorithmic flops (BASELINE.md sec.4 table): rhs={code.F_rhs} jac={code.F_jac} "
+               f"dT={code.F_dT} factor(jac+LU)={code.F_factor} solve={code.F_solve}")
+    out.append("#pragma once")
+    out.append(f"#define MBM_{X}_N {n}")
+    out.append(f"#define MBM_{X}_M {max(m, 0)}")
+    out.append(f"#define MBM_{X}_NNZ {code.nnz}")
+    out.append(f"#define MBM_{X}_NLU {code.nlu}")
+    out.append(f"#define MBM_{X}_F_RHS {code.F_rhs}")
+    out.append(f"#define MBM_{X}_F_JAC {code.F_jac}")
+    out.append(f"#define MBM_{X}_F_DT {code.F_dT}")
+    out.append(f"#define MBM_{X}_F_FACTOR {code.F_factor}")
+    out.append(f"#define MBM_{X}_F_SOLVE {code.F_solve}")
+    out.append(f"#define MBM_{X}_HAS_DT {1 if any(d != g.zero for d in code.dT_nodes) else 0}")
+    out.append(f"#define MBM_{X}_IS_ODE {1 if all(sys.mass_diag) else 0}")
+    out.append("#ifndef MB_NO_PATTERN")
+    out.append(_carray("int", f"mbm_{X}_jrow", [e[0] for e in code.jac_entries]))
+    out.append(_carray("int", f"mbm_{X}_jcol", [e[1] for e in code.jac_entries]))
+    out.append(_carray("int", f"mbm_{X}_mass", [int(v) for v in sys.mass_diag]))
+    out.append("#endif")
+    out.append("")
+    out.append(pr.function(f"MB_FN void mbm_{X}_rhs({args}, double* MB_RESTRICT du)",
+                           [(f"du[{i}]", sys.rhs[i]) for i in range(n)]))
+    out.append("")
+    out.append(pr.function(f"MB_FN void mbm_{X}_jac({args}, double* MB_RESTRICT Jnz)",
+                           [(f"Jnz[{k}]", e[2]) for k, e in enumerate(code.jac_entries)]))
+    out.append("")
+    out.append(pr.function(f"MB_FN void mbm_{X}_dT({args}, double* MB_RESTRICT dT)",
+                           [(f"dT[{i}]", code.dT_nodes[i]) for i in range(n)]))
+    out.append("")
+    lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)
+                 if g.op[node] != CONST]
+    out.append(pr.function(f"MB_FN void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
+                           lu_assign))
+    out.append("")
+    spr = Printer(code.solve_graph, {"lu": "LU[{i}]", "b": "b{i}"})
+    sol_lines = [f"MB_FN void mbm_{X}_solve(const double* MB_RESTRICT LU, double* MB_RESTRICT b) {{"]
+    for i in range(n):
+        sol_lines.append(f"  const double b{i} = b[{i}];")
+    sol_lines += spr.body(code.solve_out)
+    for i in range(n):
+        sol_lines.append(f"  b[{i}] = {spr.ref(code.solve_out[i])};")
+    sol_lines.append("}")
+    out.append("\n".join(sol_lines))
+    out.append("")
+    return "\n".join(out)

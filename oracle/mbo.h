@@ -1,0 +1,38 @@
+/* ORACLE -- test infrastructure only. Never linked into the product. */
+#ifndef MBO_H
+#define MBO_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+enum { MBO_ALG_TSIT5 = 1, MBO_ALG_RODAS5P = 2 };
+typedef struct {
+  int32_t alg;        /* MBO_ALG_* */
+  int32_t jac_mode;   /* 0 analytic (generated), 1 forward differences (`autodiff=false`, test/test_robot.jl:288) */
+  double abstol, reltol;
+  double dt0;         /* 0 = automatic */
+  double dtmin, dtmax;/* 0 = default */
+  int64_t maxiters;   /* 0 = 100000 */
+} mbo_opts;
+
+typedef void (*mbo_fn)(const double* u, const double* p, double t, const double* tb, double* out);
+typedef struct {
+  const char* name;
+  int n, m, nnz;
+  const int *jrow, *jcol, *mass;
+  mbo_fn rhs, jac, dT;
+} mbo_model;
+
+const mbo_model* mbo_find_model(const char* name);
+int mbo_model_dims(const char* name, int* n, int* m, int* nnz);
+int mbo_eval(const char* name, int what /*0 rhs,1 jac(nnz),2 dT*/, const double* u, const double* p, double t, const double* tb, double* out);
+int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass);
+int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, const double* p, const double* tb,
+                  double t0, double t1, const double* saveat, int nsave, double* out_u, double* out_tfinal, int32_t* stats);
+int mbo_solve_ensemble(const char* model, const mbo_opts* o, int64_t N, const double* u0, const double* p, const double* tb,
+                       double t0, double t1, const double* saveat, int nsave, double* out_u, double* out_tfinal,
+                       int32_t* retcode, int32_t* stats, int nthreads);
+#ifdef __cplusplus
+}
+#endif
+#endif
