@@ -144,6 +144,17 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(_carray("int", f"mbm_{X}_jcol", [e[1] for e in code.jac_entries]))
     out.append(_carray("int", f"mbm_{X}_mass", [int(v) for v in sys.mass_diag]))
     out.append("#endif")
+    words = []
+    for w0 in range(0, n, 64):
+        v = 0
+        for i in range(w0, min(n, w0 + 64)):
+            if sys.mass_diag[i]:
+                v |= 1 << (i - w0)
+        words.append(f"0x{v:x}ull")
+    out.append(f"MB_FN int mbm_{X}_isdiff(int i) {{")
+    out.append(f"  const unsigned long long w[{len(words)}] = {{{', '.join(words)}}};")
+    out.append("  return (int)((w[i >> 6] >> (i & 63)) & 1ull);")
+    out.append("}")
     out.append("")
     out.append(pr.function(f"MB_FN void mbm_{X}_rhs({args}, double* MB_RESTRICT du)",
                            [(f"du[{i}]", sys.rhs[i]) for i in range(n)]))

@@ -1,0 +1,7 @@
+// Kernel set of model 'pendulum' (generated/mbm_pendulum.h is emitted by codegen/generate.py).
+#include "mb_model_def.cuh"
+#define MB_FN static __device__ __forceinline__
+#define MB_RESTRICT __restrict__
+#define MB_NO_PATTERN
+#include "generated/mbm_pendulum.h"
+MB_DEFINE_MODEL(pendulum, 128, 4, 1)

@@ -1,0 +1,7 @@
+// Kernel set of model 'spring_damper' (generated/mbm_spring_damper.h is emitted by codegen/generate.py).
+#include "mb_model_def.cuh"
+#define MB_FN static __device__ __forceinline__
+#define MB_RESTRICT __restrict__
+#define MB_NO_PATTERN
+#include "generated/mbm_spring_damper.h"
+MB_DEFINE_MODEL(spring_damper, 128, 2, 1)

@@ -1,0 +1,15 @@
+// Registry of compiled-in model kernel sets (one entry per generated model).
+#pragma once
+#include <cuda_runtime.h>
+#include "mb_common.cuh"
+
+struct MbKernelEntry {
+  const char* name;
+  int n, m, nlu, is_ode;
+  long long flops[5];   // rhs, jac, dT, factor, solve (algorithmic)
+  // launches the ensemble kernel for `alg` on `stream`; grid sized to fill the device
+  cudaError_t (*launch)(int alg, const MbArgs& args, int sm_count, cudaStream_t stream);
+  const MbKernelEntry* next;
+};
+void mb_register_model(MbKernelEntry* e);
+const MbKernelEntry* mb_find_model(const char* name);

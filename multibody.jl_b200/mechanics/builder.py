@@ -63,8 +63,8 @@ class Tables:
     (reference: CubicSpline / LinearInterpolation with constant extrapolation,
     src/robot/path_planning.jl:191-193).
 
-    Packed layout (f64): header [t0, dt, nk] then per table `nk` values and,
-    for cubic tables, `nk` second derivatives z."""
+    Packed layout (f64): header [t0, dt, nk] then per table `nk` interleaved
+    (value, z) pairs, z = spline second derivative (0 for linear tables)."""
 
     def __init__(self):
         self.t0 = 0.0
@@ -84,10 +84,13 @@ class Tables:
         return len(self.values) - 1
 
     def pack(self) -> np.ndarray:
+        """[t0, dt, nk] then per table nk interleaved (value, z) pairs."""
         out = [np.array([self.t0, self.dt, float(self.nk)])]
         for v, z in zip(self.values, self.z):
-            out.append(v)
-            out.append(z if z is not None else np.zeros(self.nk))
+            pair = np.empty((self.nk, 2))
+            pair[:, 0] = v
+            pair[:, 1] = z if z is not None else 0.0
+            out.append(pair.ravel())
         return np.concatenate(out) if self.values else np.array([0.0, 1.0, 0.0])
 
     def eval(self, kind: str, table: int, deriv: int, t: float) -> float:

@@ -96,11 +96,14 @@ static int lu_factor(int n, double* A, int* piv) {
   return 0;
 }
 static void lu_solve_dense(int n, const double* A, const int* piv, double* b) {
+  /* rows of L were swapped as whole rows during factorisation (LAPACK convention), so
+   * all interchanges are applied to b before the forward substitution */
   for (int k = 0; k < n; k++) {
     int pk = piv[k];
     if (pk != k) { double t = b[k]; b[k] = b[pk]; b[pk] = t; }
-    for (int i = k + 1; i < n; i++) b[i] -= A[i * n + k] * b[k];
   }
+  for (int k = 0; k < n; k++)
+    for (int i = k + 1; i < n; i++) b[i] -= A[i * n + k] * b[k];
   for (int i = n - 1; i >= 0; i--) {
     double s = b[i];
     for (int j = i + 1; j < n; j++) s -= A[i * n + j] * b[j];
@@ -290,32 +293,53 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
 }
 
 /* Ensemble fan-out (SciMLBase EnsembleThreads equivalent): SoA inputs/outputs in the
- * same layout as the product's C ABI (include/mbb200.h). */
+ * same layout as the product's C ABI (include/mbb200.h).  pthreads, dynamic chunks. */
+#include <pthread.h>
+#include <stdatomic.h>
+typedef struct {
+  const mbo_model* md; const mbo_opts* o; int64_t N; const double* u0; const double* p; const double* tb;
+  double t0, t1; const double* saveat; int nsave; double* out_u; double* out_tfinal; int32_t* retcode; int32_t* stats;
+  atomic_llong next;
+} ens_t;
+
+static void* ens_worker(void* arg) {
+  ens_t* e = (ens_t*)arg;
+  const int n = e->md->n, m = e->md->m, nsave = e->nsave;
+  const int64_t N = e->N;
+  double* ul = (double*)malloc(sizeof(double) * (n + (m > 0 ? m : 1)));
+  double* pl = ul + n;
+  double* ol = (double*)malloc(sizeof(double) * (size_t)(nsave > 0 ? nsave : 1) * n);
+  for (;;) {
+    int64_t b = atomic_fetch_add(&e->next, 4);
+    if (b >= N) break;
+    int64_t hi = b + 4 < N ? b + 4 : N;
+    for (int64_t i = b; i < hi; i++) {
+      for (int j = 0; j < n; j++) ul[j] = e->u0[(size_t)j * N + i];
+      for (int j = 0; j < m; j++) pl[j] = e->p[(size_t)j * N + i];
+      int32_t st[5]; double tf;
+      for (size_t q = 0; q < (size_t)nsave * n; q++) ol[q] = NAN;
+      int rc = mbo_solve_one(e->md, e->o, ul, pl, e->tb, e->t0, e->t1, e->saveat, nsave, ol, &tf, st);
+      e->retcode[i] = rc; e->out_tfinal[i] = tf;
+      for (int s = 0; s < 5; s++) e->stats[(size_t)s * N + i] = st[s];
+      for (int s = 0; s < nsave; s++) for (int j = 0; j < n; j++) e->out_u[((size_t)s * n + j) * N + i] = ol[(size_t)s * n + j];
+    }
+  }
+  free(ul); free(ol);
+  return 0;
+}
+
 int mbo_solve_ensemble(const char* model, const mbo_opts* o, int64_t N, const double* u0 /* [n][N] */,
                        const double* p /* [m][N] */, const double* tb, double t0, double t1,
                        const double* saveat, int nsave, double* out_u /* [nsave][n][N] */,
                        double* out_tfinal, int32_t* retcode, int32_t* stats /* [5][N] */, int nthreads) {
   const mbo_model* md = mbo_find_model(model);
   if (!md) return -1;
-  const int n = md->n, m = md->m;
   if (nthreads < 1) nthreads = 1;
-#pragma omp parallel num_threads(nthreads)
-  {
-    double* ul = (double*)malloc(sizeof(double) * (n + (m > 0 ? m : 1)));
-    double* pl = ul + n;
-    double* ol = (double*)malloc(sizeof(double) * (size_t)(nsave > 0 ? nsave : 1) * n);
-#pragma omp for schedule(dynamic, 4)
-    for (int64_t i = 0; i < N; i++) {
-      for (int j = 0; j < n; j++) ul[j] = u0[(size_t)j * N + i];
-      for (int j = 0; j < m; j++) pl[j] = p[(size_t)j * N + i];
-      int32_t st[5]; double tf;
-      for (size_t q = 0; q < (size_t)nsave * n; q++) ol[q] = NAN;
-      int rc = mbo_solve_one(md, o, ul, pl, tb, t0, t1, saveat, nsave, ol, &tf, st);
-      retcode[i] = rc; out_tfinal[i] = tf;
-      for (int s = 0; s < 5; s++) stats[(size_t)s * N + i] = st[s];
-      for (int s = 0; s < nsave; s++) for (int j = 0; j < n; j++) out_u[((size_t)s * n + j) * N + i] = ol[(size_t)s * n + j];
-    }
-    free(ul); free(ol);
-  }
+  if (nthreads > 256) nthreads = 256;
+  ens_t e = {md, o, N, u0, p, tb, t0, t1, saveat, nsave, out_u, out_tfinal, retcode, stats, 0};
+  pthread_t th[256];
+  for (int k = 1; k < nthreads; k++) pthread_create(&th[k], 0, ens_worker, &e);
+  ens_worker(&e);
+  for (int k = 1; k < nthreads; k++) pthread_join(th[k], 0);
   return 0;
 }
