@@ -1,0 +1,285 @@
+#!/usr/bin/env python
+"""bench.py -- ensemble trajectories/sec on BASELINE.json's headline config (C4: Robot6DOF
+parameter sweep, Rodas5P, abstol = reltol = 1e-8, saveat 0:0.1:2, 1 Mi trajectories per GPU).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (one rank per GPU)
+    python bench.py --impl reference --gpus N ...            # CPU arm: the oracle on host cores
+
+A step = one pass of the hot path over the whole ensemble shard of this rank.
+`value` = trajectories/s with inputs resident in HBM (device time, CUDA events on the
+launching stream, max over ranks); `e2e` = the same through `mbb200_solve` with pinned HOST
+buffers (H2D + kernels + D2H inside the timed region).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import numpy as np  # noqa: E402
+
+METRIC = "ensemble trajectories/sec (Robot6DOF Rodas5P)"
+UNIT = "trajectories/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C4")
+    ap.add_argument("--trajectories", type=int, default=0, help="per-GPU ensemble size (0 = the config's full size)")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="trajectories in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(spec, N):
+    return (f"{spec.config} {spec.model} {spec.alg} abstol=reltol={spec.reltol:g} tspan={spec.tspan} "
+            f"saveat={len(spec.saveat)} trajectories_per_gpu={N}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for j, n in enumerate(names) if any(len(r) > 3 + j and r[3 + j].lower().startswith("active") for r in self.rows)]
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
+
+
+def flops_per_trajectory(flops, n, n_save, stats):
+    """Algorithmic FLOPs (BASELINE.md section 4 / SURVEY.md 8d), from the measured step counts.
+    Rodas5P: F_step = F_factor(jac + structured LU) + F_dT + 8 F_rhs + 8 F_solve + 86 n + 4 n."""
+    steps = stats[0].astype(np.float64) + stats[1].astype(np.float64)
+    f_step = flops["factor"] + flops["dT"] + 8 * flops["rhs"] + 8 * flops["solve"] + 86 * n + 4 * n
+    f_interp = (8 * 3 * 2 + 10) * n
+    dense_step = flops["jac"] + flops["dT"] + (2 * n ** 3) // 3 + 8 * flops["rhs"] + 16 * n * n + 86 * n + 4 * n
+    return steps * f_step + n_save * f_interp + 2 * flops["rhs"], f_step, dense_step, steps
+
+
+def run_reference(args):
+    """CPU arm: the oracle (CPU restatement of the reference algorithm; the Julia reference
+    itself cannot run here) on all host cores, a bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import mbpkg
+    mbpkg.load()
+    import mbo
+    from multibody_jl_b200 import ensembles
+    from multibody_jl_b200.mechanics.zoo import get_model
+    mbo.build()
+    cores = os.cpu_count() or 1
+    sample = args.cpu_sample or max(64, 16 * cores)
+    spec = ensembles.make_ensemble(args.config, sample)
+    tb = get_model(spec.model).tables.pack()
+
+    def step():
+        t = time.perf_counter()
+        r = mbo.solve(spec.model, spec.alg, spec.u0, spec.p, tb, spec.tspan, spec.saveat, abstol=spec.abstol,
+                      reltol=spec.reltol, nthreads=cores)
+        assert (r["retcode"] == 1).all()
+        return time.perf_counter() - t
+    for _ in range(args.warmup):
+        step()
+    dt = sum(step() for _ in range(args.steps))
+    v = sample * args.steps / dt
+    full = spec.n_total if not args.trajectories else args.trajectories
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(spec, full), "sample": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{sample} trajectories of the same workload per step (same RNG stream), all {cores} host threads"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference(args)
+    import torch
+    import torch.distributed as dist
+    import ctypes as C
+    import mbpkg
+    mbpkg.load()
+    from multibody_jl_b200 import _lib, api, ensembles
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    spec0 = ensembles.make_ensemble(args.config, 1)
+    N = args.trajectories or spec0.n_total
+    spec = ensembles.make_ensemble(args.config, N, offset=rank * N)
+    sys_ = api.multibody(spec.model)
+    n, m, ns = sys_.n, sys_.m, len(spec.saveat)
+    ens = api.EnsembleB200(devices=[local])
+    h = api._ensure(ens, sys_)
+    flops = h.flops()
+    alg = api.Tsit5() if spec.alg == "tsit5" else api.Rodas5P()
+    opts = api.make_opts(alg, spec.tspan, spec.abstol, spec.reltol, reduce=True)
+    L = _lib.lib()
+
+    # ---- device-resident inputs/outputs (torch is only the allocator here) --------------------
+    d_u0 = torch.from_numpy(spec.u0).to(dev)
+    d_p = torch.from_numpy(spec.p).to(dev)
+    d_out = torch.empty((ns, n, N), dtype=torch.float64, device=dev)
+    d_tf = torch.empty(N, dtype=torch.float64, device=dev)
+    d_rc = torch.empty(N, dtype=torch.int32, device=dev)
+    d_st = torch.empty((5, N), dtype=torch.int32, device=dev)
+    d_red = torch.zeros(2 * ns * n + 1, dtype=torch.float64, device=dev)
+    sv = np.ascontiguousarray(spec.saveat)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        _lib.check(L.mbb200_solve_device(h.handle, C.byref(opts), 0, N, d_u0.data_ptr(), d_p.data_ptr(), _lib.ptr(sv), ns,
+                                         d_out.data_ptr(), d_tf.data_ptr(), d_rc.data_ptr(), d_st.data_ptr(),
+                                         d_red.data_ptr()))
+        ms, nl = _lib.last_timing(0)
+        if world > 1:   # the path's only collective: the ensemble-statistic reduction
+            dist.all_reduce(d_red)
+        return ms, nl
+
+    for _ in range(args.warmup):
+        device_step()
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    t_wall = time.perf_counter()
+    dev_ms, launches = 0.0, 0
+    for _ in range(args.steps):
+        ms, nl = device_step()
+        dev_ms += ms
+        launches += nl
+    barrier()
+    wall = time.perf_counter() - t_wall
+    clk = clocks.stop()
+    tms = torch.tensor([dev_ms, wall * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    dev_ms_max, wall_ms_max = tms.tolist()
+    value = world * N * args.steps / (dev_ms_max * 1e-3)
+
+    rc = d_rc.cpu().numpy()
+    stats = d_st.cpu().numpy()
+    ok = int((rc == 1).sum())
+    ftraj, f_step, dense_step, steps = flops_per_trajectory(flops, n, ns, stats)
+    peak = _lib.measure_fp64_peak(0)
+    achieved = float(ftraj.sum()) * args.steps / (dev_ms * 1e-3)
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(spec.config)
+
+    # ---- end to end through the host-buffer ABI call (pinned host memory) ----------------------
+    h_u0 = torch.from_numpy(spec.u0).pin_memory()
+    h_p = torch.from_numpy(spec.p).pin_memory()
+    h_out = torch.empty((ns, n, N), dtype=torch.float64).pin_memory()
+    h_tf = torch.empty(N, dtype=torch.float64).pin_memory()
+    h_rc = torch.empty(N, dtype=torch.int32).pin_memory()
+    h_st = torch.empty((5, N), dtype=torch.int32).pin_memory()
+    h_red = np.zeros(2 * ns * n + 1)
+
+    def e2e_step():
+        _lib.check(L.mbb200_solve(h.handle, C.byref(opts), N, h_u0.data_ptr(), h_p.data_ptr(), _lib.ptr(sv), ns,
+                                  h_out.data_ptr(), h_tf.data_ptr(), h_rc.data_ptr(), h_st.data_ptr(), _lib.ptr(h_red)))
+        if world > 1:
+            r = torch.from_numpy(h_red).to(dev)
+            dist.all_reduce(r)
+            h_red[:] = r.cpu().numpy()
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_val = world * N * args.steps / e2e_t.item()
+    same = bool(np.array_equal(h_rc.numpy(), rc))
+    h2d = 8 * N * (n + m) + 8 * ns
+    d2h = 8 * N * n * ns + N * (8 + 4 + 20) + 8 * (2 * ns * n + 1)
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(spec, N), "full_size": N == spec.n_total,
+                   "l2": "inputs+outputs per step (%.1f GB) exceed the 126 MB L2; no flush needed" % ((h2d + d2h) / 1e9),
+                   "parallelism": f"trajectory shards x{world}, no data-path collective; NCCL all-reduce of ensemble statistics only"},
+        "wall_ms_per_step": wall_ms_max / args.steps,
+        "successful_trajectories": ok, "mean_steps_per_trajectory": float(steps.mean()),
+        "mean_rejects_per_trajectory": float(stats[1].mean()),
+        "gpu_launches": launches, "clocks": clk,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "matches_device_run": same},
+        "roofline": {"bound": "fp64", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "TFLOP/s",
+                     "frac": achieved / peak, "traffic": traffic,
+                     "peak_source": "FP64 DFMA probe measured in this run (MEASURED_PEAKS.json holds HBM/BF16 only)",
+                     "flops_per_step_structured": f_step, "flops_per_step_dense_equiv": dense_step,
+                     "hbm_gbs_algorithmic": (h2d + d2h) * args.steps / (dev_ms * 1e-3) / 1e9},
+    }
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import mbo
+        cores = os.cpu_count() or 1
+        sample = args.cpu_sample or max(64, 16 * cores)
+        cs = ensembles.make_ensemble(args.config, sample)
+        t0 = time.perf_counter()
+        r = mbo.solve(cs.model, cs.alg, cs.u0, cs.p, sys_.tables.pack(), cs.tspan, cs.saveat, abstol=cs.abstol,
+                      reltol=cs.reltol, nthreads=cores)
+        dtc = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": sample / dtc, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"first {sample} trajectories of the same workload, {cores} host threads, {dtc:.1f} s"}
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

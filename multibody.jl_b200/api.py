@@ -1,0 +1,237 @@
+"""Host-side mirror of the reference's user API for the ensemble path.
+
+    ssys  = multibody(model)                         # src/Multibody.jl:166-188
+    prob  = ODEProblem(ssys, u0map, tspan, pmap)     # test/test_robot.jl:272-287
+    eprob = EnsembleProblem(prob, prob_func=...)     # SciMLBase [ext], SURVEY.md 3.3
+    sol   = solve(eprob, Rodas5P(), EnsembleB200(), trajectories=N, saveat=..., abstol=..., reltol=...)
+
+Same names, argument meaning and error behaviour as the Julia calls; the body of
+`solve(..., EnsembleB200())` is one call into libmultibody_b200 (include/mbb200.h).
+Julia is absent in this image, so this Python module plays the part of
+`EnsembleB200.jl` (INTEGRATION.md shows the ccall twin).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Callable, Dict, Optional, Sequence, Union
+
+import numpy as np
+
+from . import _lib
+from .mechanics.builder import ReducedSystem
+from .mechanics.zoo import MODELS, get_model
+
+
+# ---- algorithms ------------------------------------------------------------------------
+@dataclass(frozen=True)
+class Tsit5:
+    id: int = _lib.ALG_TSIT5
+
+
+@dataclass(frozen=True)
+class Rodas5P:
+    """`autodiff` is accepted for signature parity (test/test_robot.jl:288 passes
+    autodiff=false); the B200 backend always uses the generated analytic Jacobian."""
+    autodiff: bool = True
+    id: int = _lib.ALG_RODAS5P
+
+
+@dataclass
+class EnsembleB200:
+    """The new `SciMLBase.EnsembleAlgorithm`.  `devices`: CUDA ordinals used by this
+    process (default: the first `n_gpus`)."""
+    n_gpus: int = 1
+    devices: Optional[Sequence[int]] = None
+
+    def ordinals(self):
+        return list(self.devices) if self.devices is not None else list(range(self.n_gpus))
+
+
+# ---- model -> problem ----------------------------------------------------------------------
+def multibody(model: Union[str, Callable[[], ReducedSystem], ReducedSystem]) -> ReducedSystem:
+    """`multibody(model)`: returns the index-reduced system.  `model` is a zoo name, a
+    builder, or an already reduced system (idempotent like `mtkcompile` on a compiled
+    system)."""
+    if isinstance(model, ReducedSystem):
+        return model
+    if isinstance(model, str):
+        if model not in MODELS:
+            raise KeyError(f"unknown model {model!r}; available: {sorted(MODELS)}")
+        return get_model(model)
+    return model()
+
+
+@dataclass
+class ODEProblem:
+    sys: ReducedSystem
+    u0: np.ndarray
+    tspan: tuple
+    p: np.ndarray
+
+    def __init__(self, sys: ReducedSystem, u0map=None, tspan=None, pmap=None):
+        self.sys = sys
+        self.u0 = sys.u0.copy()
+        self.p = sys.p0.copy()
+        self.tspan = tuple(float(x) for x in (tspan if tspan is not None else sys.meta["tspan"]))
+        for k, v in (u0map or {}).items():
+            if k in sys.state_names:
+                self.u0[sys.state_index(k)] = float(v)
+            elif k in sys.param_names:              # MTK accepts parameters in the same map
+                self.p[sys.param_index(k)] = float(v)
+            else:
+                raise KeyError(f"{k!r} is neither a state nor a parameter of {sys.name}")
+        for k, v in (pmap or {}).items():
+            self.p[sys.param_index(k)] = float(v)
+
+
+def remake(prob: ODEProblem, u0=None, p=None, tspan=None) -> ODEProblem:
+    new = ODEProblem.__new__(ODEProblem)
+    new.sys = prob.sys
+    new.u0 = np.array(u0, dtype=np.float64) if u0 is not None else prob.u0.copy()
+    new.p = np.array(p, dtype=np.float64) if p is not None else prob.p.copy()
+    new.tspan = tuple(tspan) if tspan is not None else prob.tspan
+    return new
+
+
+@dataclass
+class EnsembleProblem:
+    """`prob_func(prob, i, repeat) -> prob` as in SciMLBase.  For large ensembles pass
+    `u0_matrix` [n][N] and/or `p_matrix` [m][N] directly (the materialised result of
+    running prob_func on the host)."""
+    prob: ODEProblem
+    prob_func: Optional[Callable] = None
+    u0_matrix: Optional[np.ndarray] = None
+    p_matrix: Optional[np.ndarray] = None
+
+    def materialise(self, N: int):
+        n, m = self.prob.sys.n, self.prob.sys.m
+        U = np.empty((n, N))
+        P = np.empty((max(m, 1), N))
+        U[:] = self.prob.u0[:, None]
+        P[:m] = self.prob.p[:, None] if m else 0.0
+        if self.u0_matrix is not None:
+            U[:] = np.asarray(self.u0_matrix, dtype=np.float64).reshape(n, N)
+        if self.p_matrix is not None and m:
+            P[:m] = np.asarray(self.p_matrix, dtype=np.float64).reshape(m, N)
+        if self.prob_func is not None:
+            for i in range(N):
+                q = self.prob_func(self.prob, i, 0)
+                U[:, i] = q.u0
+                if m:
+                    P[:m, i] = q.p
+        return U, P
+
+
+# ---- solution -----------------------------------------------------------------------------
+@dataclass
+class TrajectorySolution:
+    t: np.ndarray
+    u: np.ndarray            # [n_save][n]
+    retcode: int
+    stats: Dict[str, int]
+    sys: ReducedSystem
+
+    def __getitem__(self, name: str) -> np.ndarray:
+        return self.u[:, self.sys.state_index(name)]
+
+
+def successful_retcode(sol) -> bool:
+    rc = sol.retcode
+    return bool(np.all(np.asarray(rc) == 1))
+
+
+@dataclass
+class EnsembleSolution:
+    sys: ReducedSystem
+    t: np.ndarray            # saveat
+    u: np.ndarray            # [n_save][n][N]
+    t_final: np.ndarray
+    retcode: np.ndarray
+    stats: np.ndarray        # [5][N]: naccept, nreject, nf, njac, nsolve
+    reduction: Optional[Dict[str, np.ndarray]] = None
+    kernel_ms: float = 0.0
+    gpu_launches: int = 0
+
+    def __len__(self):
+        return self.u.shape[2]
+
+    def __getitem__(self, i: int) -> TrajectorySolution:
+        names = ("naccept", "nreject", "nf", "njac", "nsolve")
+        return TrajectorySolution(self.t, self.u[:, :, i], int(self.retcode[i]),
+                                  {k: int(self.stats[j, i]) for j, k in enumerate(names)}, self.sys)
+
+    def state(self, name: str) -> np.ndarray:
+        """[n_save][N] values of one named state."""
+        return self.u[:, self.sys.state_index(name), :]
+
+
+_handles: Dict[str, _lib.ModelHandle] = {}
+_devices = None
+
+
+def _ensure(ens: EnsembleB200, sys: ReducedSystem) -> _lib.ModelHandle:
+    global _devices
+    ords = ens.ordinals()
+    if _devices is None:
+        _lib.init_devices(ords)
+        _devices = ords
+    elif _devices != ords:
+        raise _lib.Mbb200Error(-2, f"library already initialised on devices {_devices}; got {ords}")
+    if sys.name not in _handles:
+        _handles[sys.name] = _lib.ModelHandle(sys.name, sys.n, sys.m, sys.tables.pack())
+    return _handles[sys.name]
+
+
+def shutdown():
+    global _devices
+    for h in _handles.values():
+        h.free()
+    _handles.clear()
+    if _devices is not None:
+        _lib.lib().mbb200_shutdown()
+        _devices = None
+
+
+def make_opts(alg, tspan, abstol=1e-6, reltol=1e-3, dt=0.0, dtmin=0.0, dtmax=0.0, maxiters=0, reduce=False):
+    return _lib.Opts(alg.id, _lib.FLAG_REDUCE if reduce else 0, tspan[0], tspan[1], abstol, reltol,
+                     dt, dtmin, dtmax, int(maxiters))
+
+
+def solve(eprob: Union[EnsembleProblem, ODEProblem], alg, ensemblealg: Optional[EnsembleB200] = None, *,
+          trajectories: int = 1, saveat=None, abstol: float = 1e-6, reltol: float = 1e-3, dt: float = 0.0,
+          dtmin: float = 0.0, dtmax: float = 0.0, maxiters: int = 0, reduction: bool = False) -> EnsembleSolution:
+    """`solve(eprob, alg, EnsembleB200(); trajectories, saveat, abstol, reltol, ...)`.
+    Defaults are SciML's (abstol 1e-6, reltol 1e-3).  A plain ODEProblem is run as an
+    ensemble of one.  `reduction=True` also returns count/mean/variance statistics."""
+    if isinstance(eprob, ODEProblem):
+        eprob = EnsembleProblem(eprob)
+    ens = ensemblealg or EnsembleB200()
+    sys = eprob.prob.sys
+    N = int(trajectories)
+    h = _ensure(ens, sys)
+    U, P = eprob.materialise(N)
+    tspan = eprob.prob.tspan
+    sv = np.ascontiguousarray(np.atleast_1d(np.asarray(saveat if saveat is not None else [tspan[1]], dtype=np.float64)))
+    ns, n = len(sv), sys.n
+    out = np.empty((ns, n, N))
+    tf = np.empty(N)
+    rc = np.zeros(N, np.int32)
+    st = np.zeros((5, N), np.int32)
+    red = np.zeros(2 * ns * n + 1) if reduction else None
+    o = make_opts(alg, tspan, abstol, reltol, dt, dtmin, dtmax, maxiters, reduction)
+    _lib.check(_lib.lib().mbb200_solve(h.handle, C.byref(o), N, _lib.ptr(U), _lib.ptr(P) if sys.m else None,
+                                       _lib.ptr(sv), ns, _lib.ptr(out), _lib.ptr(tf), _lib.ptr(rc), _lib.ptr(st),
+                                       _lib.ptr(red) if reduction else None))
+    ms, nl = 0.0, 0
+    for g in range(len(ens.ordinals())):
+        m_, l_ = _lib.last_timing(g)
+        ms, nl = max(ms, m_), nl + l_
+    redd = None
+    if reduction:
+        cnt = red[0]
+        s1 = red[1:1 + ns * n].reshape(ns, n)
+        s2 = red[1 + ns * n:].reshape(ns, n)
+        redd = dict(count=cnt, sum=s1, sumsq=s2, mean=s1 / max(cnt, 1.0),
+                    var=np.maximum(s2 / max(cnt, 1.0) - (s1 / max(cnt, 1.0)) ** 2, 0.0), raw=red)
+    return EnsembleSolution(sys, sv, out, tf, rc, st, redd, ms, nl)

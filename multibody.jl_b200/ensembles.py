@@ -1,0 +1,86 @@
+"""The BASELINE.json configs as concrete synthetic ensembles.
+
+All draws come from a counter-based generator (splitmix64 keyed by seed, trajectory index
+and parameter slot), so any shard of any size reproduces the same values on every rank
+and on the CPU oracle without storing or communicating them.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from .mechanics.zoo import get_model
+
+SEED = 20261104
+
+
+def _splitmix64(x: np.ndarray) -> np.ndarray:
+    x = (x + np.uint64(0x9E3779B97F4A7C15)).astype(np.uint64)
+    z = x.copy()
+    z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return z ^ (z >> np.uint64(31))
+
+
+def uniform(index: np.ndarray, slot: int, lo: float, hi: float, seed: int = SEED) -> np.ndarray:
+    """U[lo,hi) for trajectory indices `index` (int64 array) and parameter slot `slot`."""
+    with np.errstate(over="ignore"):
+        key = _splitmix64(np.uint64(seed) + np.uint64(0x632BE59BD9B4E019) * np.uint64(slot + 1))
+        z = _splitmix64(index.astype(np.uint64) * np.uint64(0xD1342543DE82EF95) + key)
+    return lo + (hi - lo) * ((z >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0))
+
+
+@dataclass
+class EnsembleSpec:
+    config: str
+    model: str
+    alg: str                 # "tsit5" | "rodas5p"
+    tspan: tuple
+    saveat: np.ndarray
+    abstol: float
+    reltol: float
+    u0: np.ndarray           # [n][N]
+    p: np.ndarray            # [m][N]
+    n_total: int             # size the BASELINE config names
+
+
+def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> EnsembleSpec:
+    """Trajectories [offset, offset+N) of config C1..C4 (N defaults to the full size)."""
+    config = config.upper()
+    if config == "C1":      # pendulum, 1024 initial angles, Tsit5 (docs/src/examples/pendulum.md:25-68)
+        total, model, alg, tol = 1024, "pendulum", "tsit5", 1e-8
+        saveat = np.linspace(0.0, 10.0, 101)
+    elif config == "C2":    # spring-damper, 1M parameter sets, Tsit5, 100 saves (spring_damper_system.md:21-63)
+        total, model, alg, tol = 1 << 20, "spring_damper", "tsit5", 1e-8
+        saveat = 0.05 * np.arange(1, 101)
+    elif config == "C4":    # Robot6DOF parameter sweep, 1M, Rodas5P reltol 1e-8 (test/test_robot.jl:268-288)
+        total, model, alg, tol = 1 << 20, "robot6dof", "rodas5p", 1e-8
+        saveat = np.linspace(0.0, 2.0, 21)
+    else:
+        raise KeyError(f"config {config} is not built yet (C1, C2, C4 are)")
+    N = total if N is None else int(N)
+    sys = get_model(model)
+    idx = np.arange(offset, offset + N, dtype=np.int64)
+    U = np.repeat(sys.u0[:, None], N, axis=1)
+    P = np.repeat(sys.p0[:, None], N, axis=1) if sys.m else np.zeros((0, N))
+    if config == "C1":
+        U[sys.state_index("joint.phi")] = -np.pi + 2.0 * np.pi * (idx + 0.5) / 1024.0
+    elif config == "C2":
+        c = uniform(idx, 0, 10.0, 100.0)
+        d = uniform(idx, 1, 0.5, 5.0)
+        m = uniform(idx, 2, 0.5, 2.0)
+        P[sys.param_index("spring1.c")] = c
+        P[sys.param_index("spring2.c")] = c
+        P[sys.param_index("damper1.d")] = d
+        P[sys.param_index("body1.m")] = m
+        P[sys.param_index("body2.m")] = m
+    elif config == "C4":
+        P[sys.param_index("mechanics.load.m")] = uniform(idx, 0, 5.0, 25.0)
+        for a in range(6):
+            P[sys.param_index(f"axis{a+1}.controller.kp")] = uniform(idx, 1 + 3 * a, 3.0, 8.0)
+            P[sys.param_index(f"axis{a+1}.controller.ks")] = uniform(idx, 2 + 3 * a, 0.3, 0.8)
+            P[sys.param_index(f"axis{a+1}.controller.Ts")] = uniform(idx, 3 + 3 * a, 0.03, 0.08)
+    return EnsembleSpec(config, model, alg, tuple(sys.meta["tspan"]), saveat, tol, tol,
+                        np.ascontiguousarray(U), np.ascontiguousarray(P), total)

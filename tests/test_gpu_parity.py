@@ -1,0 +1,95 @@
+"""GPU parity: libmultibody_b200 (through the C ABI) vs the CPU oracle on the same seeded
+inputs.  Tolerance (BASELINE.json north_star): saved trajectories and final states agree
+within 1e-6 relative at reltol = abstol = 1e-8, FP64.  Step counts are reported, not asserted
+exactly (the two sides differ in FMA contraction and LU pivot order)."""
+import numpy as np
+import pytest
+
+from multibody_jl_b200 import api, ensembles
+from multibody_jl_b200.mechanics.zoo import get_model
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-6   # stated tolerance of the north star
+
+
+def _run_gpu(spec, **kw):
+    sys_ = api.multibody(spec.model)
+    prob = api.ODEProblem(sys_, tspan=spec.tspan)
+    eprob = api.EnsembleProblem(prob, u0_matrix=spec.u0, p_matrix=spec.p)
+    alg = api.Tsit5() if spec.alg == "tsit5" else api.Rodas5P()
+    return api.solve(eprob, alg, api.EnsembleB200(), trajectories=spec.u0.shape[1], saveat=spec.saveat,
+                     abstol=spec.abstol, reltol=spec.reltol, **kw)
+
+
+def _run_oracle(oracle, spec, nthreads=8):
+    sys_ = get_model(spec.model)
+    return oracle.solve(spec.model, spec.alg, spec.u0, spec.p, sys_.tables.pack(), spec.tspan, spec.saveat,
+                        abstol=spec.abstol, reltol=spec.reltol, nthreads=nthreads)
+
+
+def _compare(sol, ref, rtol=RTOL):
+    assert np.array_equal(sol.retcode, ref["retcode"])
+    assert np.all(sol.retcode == 1)
+    scale = np.maximum(np.abs(ref["u"]).max(axis=(0, 2), keepdims=True), 1e-3)   # per-state scale
+    err = np.abs(sol.u - ref["u"]) / scale
+    assert np.isfinite(err).all()
+    assert err.max() < rtol, f"max scaled error {err.max():.3e}"
+    np.testing.assert_allclose(sol.t_final, ref["t"], rtol=0, atol=1e-12)
+    # step counts: reported side by side, loosely bounded
+    ga, oa = sol.stats[0].astype(float), ref["stats"][0].astype(float)
+    print(f"naccept gpu mean {ga.mean():.1f} oracle mean {oa.mean():.1f}; nreject gpu {sol.stats[1].mean():.2f} "
+          f"oracle {ref['stats'][1].mean():.2f}; max err {err.max():.2e}")
+    assert abs(ga.mean() - oa.mean()) <= 0.02 * oa.mean() + 2
+
+
+@pytest.mark.parametrize("config,N", [("C1", 1024), ("C2", 2048), ("C4", 256)])
+def test_config_parity(oracle, config, N):
+    spec = ensembles.make_ensemble(config, N)
+    _compare(_run_gpu(spec), _run_oracle(oracle, spec))
+
+
+def test_pendulum_rodas5p_parity(oracle):
+    spec = ensembles.make_ensemble("C1", 512)
+    spec.alg = "rodas5p"
+    _compare(_run_gpu(spec), _run_oracle(oracle, spec))
+
+
+def test_ragged_sizes_and_empty(oracle):
+    for N in (1, 31, 33, 257):
+        spec = ensembles.make_ensemble("C2", N, offset=7)
+        _compare(_run_gpu(spec), _run_oracle(oracle, spec))
+    spec = ensembles.make_ensemble("C1", 0)
+    sol = _run_gpu(spec)
+    assert sol.u.shape == (101, 2, 0)
+
+
+def test_failed_trajectories_do_not_fail_the_call(oracle):
+    # maxiters too small: every trajectory must come back with retcode MaxIters and NaN tails
+    spec = ensembles.make_ensemble("C1", 64)
+    sol = _run_gpu(spec, maxiters=10)
+    assert np.all(sol.retcode == 4)
+    assert np.isnan(sol.u[-1]).all() and np.isfinite(sol.u[0]).all()
+    ref = oracle.solve(spec.model, spec.alg, spec.u0, spec.p, get_model(spec.model).tables.pack(), spec.tspan,
+                       spec.saveat, abstol=1e-8, reltol=1e-8, maxiters=10)
+    assert np.array_equal(sol.retcode, ref["retcode"])
+    np.testing.assert_allclose(sol.t_final, ref["t"], rtol=1e-6)   # step sizes differ at rounding level (FMA contraction)
+
+
+def test_reduction_matches_host_statistics():
+    spec = ensembles.make_ensemble("C2", 1000)
+    sol = _run_gpu(spec, reduction=True)
+    assert sol.reduction["count"] == 1000
+    np.testing.assert_allclose(sol.reduction["sum"], sol.u.sum(axis=2), rtol=1e-10, atol=1e-9)
+    np.testing.assert_allclose(sol.reduction["sumsq"], (sol.u ** 2).sum(axis=2), rtol=1e-10, atol=1e-9)
+
+
+def test_full_size_properties_c4_sample():
+    """Size-independent properties at BASELINE scale shapes: robot end pose reaches q1 and
+    tracking error stays below the reference's own bound (test/test_robot.jl:324-325)."""
+    spec = ensembles.make_ensemble("C4", 4096, offset=500000)
+    sol = _run_gpu(spec)
+    assert np.all(sol.retcode == 1)
+    q1 = np.deg2rad([60.0, -70.0, -35.0, 45.0, 110.0, 45.0])
+    for a in range(6):
+        end = sol.state(f"mechanics.r{a+1}.phi")[-1]
+        assert np.abs(end - q1[a]).max() < 0.01
