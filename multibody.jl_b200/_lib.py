@@ -13,7 +13,7 @@ import subprocess
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libmultibody_b200.so")
+LIB_PATH = os.environ.get("MBB200_LIB") or os.path.join(HERE, "lib", "libmultibody_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
 ALG_TSIT5, ALG_RODAS5P = 1, 2

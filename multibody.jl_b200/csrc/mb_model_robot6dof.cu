@@ -4,4 +4,11 @@
 #define MB_RESTRICT __restrict__
 #define MB_NO_PATTERN
 #include "generated/mbm_robot6dof.h"
-MB_DEFINE_MODEL(robot6dof, 128, 1, 0)
+#ifndef MB_R_BLOCK
+#define MB_R_BLOCK 128
+#endif
+#ifndef MB_R_MINB
+#define MB_R_MINB 1
+#endif
+#define MB_EXPAND(...) MB_DEFINE_MODEL(__VA_ARGS__)
+MB_EXPAND(robot6dof, MB_R_BLOCK, MB_R_MINB, 0)
