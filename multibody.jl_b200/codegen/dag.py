@@ -203,6 +203,54 @@ class Graph:
                 stack.append(b[n]); stack.append(c[n])
         return sorted(seen)
 
+    def schedule(self, outs: Sequence[int]) -> List[int]:
+        """Evaluation order for straight-line code: depth-first post-order from the
+        outputs, heavier operand first (Sethi-Ullman flavoured).  Compared with plain
+        creation order this keeps producers next to their consumers, which shortens
+        live ranges and cuts register spills in the emitted CUDA."""
+        op, a, b, c = self.op, self.a, self.b, self.c
+        need = self.reachable(outs)
+        weight: Dict[int, int] = {}
+        for n in need:                       # ascending = topological
+            o = op[n]
+            if o in (CONST, INPUT):
+                weight[n] = 0
+            elif o in (ADD, SUB, MUL, DIV, ATAN2, MIN, MAX):
+                weight[n] = 1 + weight[a[n]] + weight[b[n]]
+            elif o == SELGE:
+                weight[n] = 1 + weight[a[n]] + weight[b[n]] + weight[c[n]]
+            else:
+                weight[n] = 1 + weight[a[n]]
+            if weight[n] > 1 << 40:
+                weight[n] = 1 << 40
+        done = set()
+        order: List[int] = []
+        for root in outs:
+            stack = [(root, False)]
+            while stack:
+                n, expanded = stack.pop()
+                if n in done:
+                    continue
+                o = op[n]
+                if o in (CONST, INPUT):
+                    done.add(n); order.append(n)
+                    continue
+                if expanded:
+                    done.add(n); order.append(n)
+                    continue
+                stack.append((n, True))
+                if o in (ADD, SUB, MUL, DIV, ATAN2, MIN, MAX):
+                    kids = [a[n], b[n]]
+                elif o == SELGE:
+                    kids = [a[n], b[n], c[n]]
+                else:
+                    kids = [a[n]]
+                kids.sort(key=lambda k: weight[k])      # lightest pushed first -> heaviest visited first
+                for kid in kids:
+                    if kid not in done:
+                        stack.append((kid, False))
+        return order
+
     def flops(self, outs: Iterable[int]) -> int:
         """Algorithmic flop count.  An ADD/SUB with a MUL
         operand still counts 2 in total (fma = 2), so no special case."""

@@ -23,8 +23,9 @@ class Printer:
     """Prints the nodes needed for a set of outputs as `const double xN = ...;`."""
 
     def __init__(self, g: Graph, input_fmt: Dict[str, str], interp_fmt: str =
-                 "mb_interp_{kind}{deriv}(tb, {table}, {t})"):
+                 "mb_interp_{kind}{deriv}(tb, {table}, {t})", scheduled: bool = True):
         self.g = g
+        self.scheduled = scheduled
         self.input_fmt = input_fmt
         self.interp_fmt = interp_fmt
 
@@ -41,49 +42,75 @@ class Printer:
             return f"(-{self.ref(g.a[n])})"
         return f"x{n}"
 
+    def _line(self, n: int, indent: str):
+        g = self.g
+        r = self.ref
+        o = g.op[n]
+        if o in (CONST, INPUT, NEG):
+            return None
+        a, b, c = g.a[n], g.b[n], g.c[n]
+        if o in (ADD, SUB, MUL, DIV):
+            e = f"{r(a)} {'+-*/'[o - ADD]} {r(b)}"
+        elif o == SIN:
+            e = f"sin({r(a)})"
+        elif o == COS:
+            e = f"cos({r(a)})"
+        elif o == SQRT:
+            e = f"sqrt({r(a)})"
+        elif o == ABS:
+            e = f"fabs({r(a)})"
+        elif o == ATAN2:
+            e = f"atan2({r(a)}, {r(b)})"
+        elif o == MIN:
+            e = f"fmin({r(a)}, {r(b)})"
+        elif o == MAX:
+            e = f"fmax({r(a)}, {r(b)})"
+        elif o == SELGE:
+            e = f"(({r(a)} >= 0.0) ? {r(b)} : {r(c)})"
+        elif o == INTERP:
+            kind, table, deriv = g.payload[n]
+            e = self.interp_fmt.format(kind=kind, deriv=deriv, table=table, t=r(a))
+        else:
+            raise NotImplementedError(o)
+        return f"{indent}const double x{n} = {e};"
+
     def body(self, outs: Sequence[int], indent: str = "  ") -> List[str]:
         g = self.g
         lines: List[str] = []
-        r = self.ref
-        for n in g.reachable(outs):
-            o = g.op[n]
-            if o in (CONST, INPUT, NEG):
-                continue
-            a, b, c = g.a[n], g.b[n], g.c[n]
-            if o in (ADD, SUB, MUL, DIV):
-                e = f"{r(a)} {'+-*/'[o - ADD]} {r(b)}"
-            elif o == SIN:
-                e = f"sin({r(a)})"
-            elif o == COS:
-                e = f"cos({r(a)})"
-            elif o == SQRT:
-                e = f"sqrt({r(a)})"
-            elif o == ABS:
-                e = f"fabs({r(a)})"
-            elif o == ATAN2:
-                e = f"atan2({r(a)}, {r(b)})"
-            elif o == MIN:
-                e = f"fmin({r(a)}, {r(b)})"
-            elif o == MAX:
-                e = f"fmax({r(a)}, {r(b)})"
-            elif o == SELGE:
-                e = f"(({r(a)} >= 0.0) ? {r(b)} : {r(c)})"
-            elif o == INTERP:
-                kind, table, deriv = g.payload[n]
-                e = self.interp_fmt.format(kind=kind, deriv=deriv, table=table, t=r(a))
-            else:
-                raise NotImplementedError(o)
-            lines.append(f"{indent}const double x{n} = {e};")
+        for n in (g.schedule(outs) if self.scheduled else g.reachable(outs)):
+            ln = self._line(n, indent)
+            if ln is not None:
+                lines.append(ln)
         return lines
 
     def function(self, signature: str, assigns: Sequence[Tuple[str, int]],
                  indent: str = "  ") -> str:
-        """`assigns` = [(lhs C expression, node)], written after all temporaries."""
-        outs = [n for _, n in assigns]
+        """`assigns` = [(lhs C expression, node)].  With scheduling on, each output is
+        stored as soon as its value exists (short live ranges); otherwise all stores
+        follow the temporaries."""
+        g = self.g
         lines = [signature + " {"]
-        lines += self.body(outs, indent)
-        for lhs, n in assigns:
-            lines.append(f"{indent}{lhs} = {self.ref(n)};")
+        if not self.scheduled:
+            lines += self.body([n for _, n in assigns], indent)
+            for lhs, n in assigns:
+                lines.append(f"{indent}{lhs} = {self.ref(n)};")
+        else:
+            order = g.schedule([n for _, n in assigns])
+            pos = {n: i for i, n in enumerate(order)}
+            by_node: Dict[int, List[str]] = {}
+            for lhs, n in assigns:
+                by_node.setdefault(n, []).append(lhs)
+            emitted_lhs = set()
+            for n in order:
+                ln = self._line(n, indent)
+                if ln is not None:
+                    lines.append(ln)
+                for lhs in by_node.get(n, ()):
+                    lines.append(f"{indent}{lhs} = {self.ref(n)};")
+                    emitted_lhs.add(lhs)
+            for lhs, n in assigns:          # outputs that are constants / inputs
+                if lhs not in emitted_lhs:
+                    lines.append(f"{indent}{lhs} = {self.ref(n)};")
         lines.append("}")
         return "\n".join(lines)
 

@@ -62,7 +62,12 @@ class ModelCode:
         self.lu_nodes: List[int] = []
         self.lu_slots: Dict[Tuple[str, int, int], int] = {}
 
+        self.lu_const: Dict[Tuple[str, int, int], float] = {}
+
         def slot(kind, k, idx, node):
+            if g.op[node] == CONST:          # structural constants take no storage
+                self.lu_const[(kind, k, idx)] = g.val[node]
+                return
             self.lu_slots[(kind, k, idx)] = len(self.lu_nodes)
             self.lu_nodes.append(node)
         for step, (pr, pc) in enumerate(order):
@@ -77,11 +82,9 @@ class ModelCode:
         self.solve_graph = sg
 
         def lu_in(kind, k, idx):
-            s = self.lu_slots[(kind, k, idx)]
-            node = self.lu_nodes[s]
-            if g.op[node] == CONST:             # structural constants need no load
-                return sg.const(g.val[node])
-            return sg.input("lu", s)
+            if (kind, k, idx) in self.lu_const:
+                return sg.const(self.lu_const[(kind, k, idx)])
+            return sg.input("lu", self.lu_slots[(kind, k, idx)])
         sL = {k: [(i, lu_in("l", k, i)) for i, _ in L[k]] for k in range(n)}
         sU = {k: [(j, lu_in("u", k, j)) for j, _ in U[k]] for k in range(n)}
         sD = {k: lu_in("d", k, 0) for k in range(n)}
@@ -165,8 +168,7 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(pr.function(f"MB_FN void mbm_{X}_dT({args}, double* MB_RESTRICT dT)",
                            [(f"dT[{i}]", code.dT_nodes[i]) for i in range(n)]))
     out.append("")
-    lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)
-                 if g.op[node] != CONST]
+    lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)]
     out.append(pr.function(f"MB_FN void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     out.append("")

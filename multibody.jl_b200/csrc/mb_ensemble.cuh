@@ -156,7 +156,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
         if (!(t < a.t1)) rc = RC_SUCCESS;
       }
     }
-    if (!__any_sync(FULL, active)) break;
+    // block-wide barrier + vote: keeps the warps of a CTA in step, so the (large) straight-line
+    // instruction stream is fetched once per CTA per step instead of once per warp
+    if (!__syncthreads_or(active)) break;
     if (active && rc == RC_DEFAULT) {
       ++iter;
       if (iter > maxiters) rc = RC_MAXITERS;
