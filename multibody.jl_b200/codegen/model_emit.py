@@ -41,7 +41,14 @@ class ModelCode:
         u_nodes = sys.u_nodes()
         t_node = sys.t_node()
         # --- analytic Jacobian (sparse) and time derivative -------------------
-        J = g.diff(sys.rhs, u_nodes)
+        override = getattr(sys, "jac_rows", None) or {}
+        plain_rows = [i for i in range(n) if i not in override]
+        Jp = g.diff([sys.rhs[i] for i in plain_rows], u_nodes)
+        J = [None] * n
+        for i, r in zip(plain_rows, Jp):
+            J[i] = r
+        for i, r in override.items():
+            J[i] = {j: v for j, v in r.items() if v != g.zero}
         self.jac_entries: List[Tuple[int, int, int]] = []      # (row, col, node)
         for i in range(n):
             for j in sorted(J[i]):

@@ -5,7 +5,7 @@
 #define MB_NO_PATTERN
 #include "generated/mbm_robot6dof.h"
 #ifndef MB_R_BLOCK
-#define MB_R_BLOCK 128
+#define MB_R_BLOCK 256
 #endif
 #ifndef MB_R_MINB
 #define MB_R_MINB 1

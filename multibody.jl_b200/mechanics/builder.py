@@ -29,6 +29,9 @@ class ReducedSystem:
     tables: "Tables"
     observed: Dict[str, int] = field(default_factory=dict)
     meta: Dict[str, object] = field(default_factory=dict)
+    # optional hand-derived Jacobian rows {state row: {col: node}} (must equal d rhs/d u;
+    # checked against plain differentiation in tests/test_codegen.py)
+    jac_rows: Dict[int, Dict[int, int]] = field(default_factory=dict)
 
     @property
     def n(self) -> int:
@@ -161,6 +164,7 @@ class ModelBuilder:
         self.rhs: Dict[int, int] = {}
         self.tables = Tables()
         self.observed: Dict[str, int] = {}
+        self.jac_rows: Dict[int, Dict[int, int]] = {}
         self._nacc = 0
         self.t = Ex(self.g, self.g.input("t", 0))
 
@@ -210,4 +214,4 @@ class ModelBuilder:
                              np.array(self.u0), np.array(self.mass, dtype=np.int32),
                              list(self.param_names), np.array(self.p0),
                              [self.rhs[i] for i in range(n)], self.tables,
-                             dict(self.observed), dict(meta))
+                             dict(self.observed), dict(meta), dict(self.jac_rows))
