@@ -21,11 +21,15 @@ typedef struct {
   int n, m, nnz;
   const int *jrow, *jcol, *mass;
   mbo_fn rhs, jac, dT;
+  int nlu;            /* slots of the product's generated structured LU (checked in tests only) */
+  void (*factor)(const double* u, const double* p, double t, const double* tb, double c, double* LU);
+  void (*solve)(const double* LU, double* b);
 } mbo_model;
 
 const mbo_model* mbo_find_model(const char* name);
 int mbo_model_dims(const char* name, int* n, int* m, int* nnz);
 int mbo_eval(const char* name, int what /*0 rhs,1 jac(nnz),2 dT*/, const double* u, const double* p, double t, const double* tb, double* out);
+int mbo_factor_solve(const char* name, const double* u, const double* p, double t, const double* tb, double c, double* b);
 int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass);
 int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, const double* p, const double* tb,
                   double t0, double t1, const double* saveat, int nsave, double* out_u, double* out_tfinal, int32_t* stats);

@@ -19,8 +19,9 @@ class Opts(C.Structure):
 
 
 def build(force=False):
-    if force or not os.path.exists(LIB):
-        subprocess.check_call(["make", "-C", HERE], stdout=subprocess.DEVNULL)
+    if force and os.path.exists(LIB):
+        os.remove(LIB)
+    subprocess.check_call(["make", "-C", HERE], stdout=subprocess.DEVNULL)   # no-op when up to date
     return LIB
 
 
@@ -54,6 +55,22 @@ def eval_fn(model, what, u, p, t, tb):
     tb = np.ascontiguousarray(tb, dtype=np.float64)
     lib().mbo_eval(model.encode(), what, _dp(u), _dp(p), C.c_double(t), _dp(tb), _dp(out))
     return out
+
+
+def factor_solve(model, u, p, t, tb, c, b):
+    """x = (c*M - J)^-1 b through the product's generated factor/solve code (CPU compile)."""
+    x = np.array(b, dtype=np.float64)
+    u = np.ascontiguousarray(u, dtype=np.float64); p = np.ascontiguousarray(p, dtype=np.float64)
+    tb = np.ascontiguousarray(tb, dtype=np.float64)
+    lib().mbo_factor_solve(model.encode(), _dp(u), _dp(p), C.c_double(t), _dp(tb), C.c_double(c), _dp(x))
+    return x
+
+
+def mass_diag(model):
+    n, m, nnz = dims(model)
+    jr = np.zeros(nnz, np.int32); jc = np.zeros(nnz, np.int32); ms = np.zeros(n, np.int32)
+    lib().mbo_pattern(model.encode(), _ip(jr), _ip(jc), _ip(ms))
+    return ms
 
 
 def jac_dense(model, u, p, t, tb):

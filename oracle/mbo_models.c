@@ -17,7 +17,7 @@
 #endif
 
 #define ENTRY(X) {#X, MBM_##X##_N, MBM_##X##_M, MBM_##X##_NNZ, mbm_##X##_jrow, mbm_##X##_jcol, mbm_##X##_mass, \
-                  mbm_##X##_rhs, mbm_##X##_jac, mbm_##X##_dT}
+                  mbm_##X##_rhs, mbm_##X##_jac, mbm_##X##_dT, MBM_##X##_NLU, mbm_##X##_factor, mbm_##X##_solve}
 static const mbo_model MODELS[] = {
   ENTRY(pendulum), ENTRY(spring_damper), ENTRY(robot6dof),
 #ifdef MBO_HAVE_FOURBAR
@@ -51,5 +51,18 @@ int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass) {
   memcpy(jrow, md->jrow, sizeof(int) * md->nnz);
   memcpy(jcol, md->jcol, sizeof(int) * md->nnz);
   memcpy(mass, md->mass, sizeof(int) * md->n);
+  return 0;
+}
+
+/* Checks the product's generated structured factor/solve pair on the CPU (tests only; the
+ * oracle's own integrator uses the dense pivoted LU above it, never these). */
+#include <stdlib.h>
+int mbo_factor_solve(const char* name, const double* u, const double* p, double t, const double* tb, double c, double* b) {
+  const mbo_model* md = mbo_find_model(name);
+  if (!md) return -1;
+  double* LU = (double*)calloc(md->nlu > 0 ? md->nlu : 1, sizeof(double));
+  md->factor(u, p, t, tb, c, LU);
+  md->solve(LU, b);
+  free(LU);
   return 0;
 }
