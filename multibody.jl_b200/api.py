@@ -229,9 +229,6 @@ def solve(eprob: Union[EnsembleProblem, ODEProblem], alg, ensemblealg: Optional[
         ms, nl = max(ms, m_), nl + l_
     redd = None
     if reduction:
-        cnt = red[0]
-        s1 = red[1:1 + ns * n].reshape(ns, n)
-        s2 = red[1 + ns * n:].reshape(ns, n)
-        redd = dict(count=cnt, sum=s1, sumsq=s2, mean=s1 / max(cnt, 1.0),
-                    var=np.maximum(s2 / max(cnt, 1.0) - (s1 / max(cnt, 1.0)) ** 2, 0.0), raw=red)
+        from .distributed import allreduce_statistics, finalize_statistics
+        redd = finalize_statistics(allreduce_statistics(red), ns, n)   # no-op outside torch.distributed
     return EnsembleSolution(sys, sv, out, tf, rc, st, redd, ms, nl)

@@ -1,0 +1,167 @@
+"""Pins the oracle (CPU restatement of the reference algorithm) before anything trusts it:
+golden vectors from an independent integrator (scipy DOP853 / Radau, tests/golden/), closed-form
+models, convergence order of both methods, the reference's own known answers (SURVEY.md
+Appendix D) and a second derivation of the robot model (tests/ref_models.py)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from multibody_jl_b200 import ensembles
+from multibody_jl_b200.mechanics.zoo import get_model
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+KA = json.load(open(os.path.join(GOLD, "reference_known_answers.json")))
+
+
+def _solve(oracle, spec, sel=None, **kw):
+    sysm = get_model(spec.model)
+    u0 = spec.u0 if sel is None else spec.u0[:, sel]
+    p = spec.p if sel is None else spec.p[:, sel]
+    kw.setdefault("abstol", spec.abstol)
+    kw.setdefault("reltol", spec.reltol)
+    return oracle.solve(spec.model, kw.pop("alg", spec.alg), u0, p, sysm.tables.pack(), spec.tspan, spec.saveat, **kw)
+
+
+def _scaled_err(u, gold):
+    """u [ns][n][N] vs gold [N][ns][n]; scaled per state by its range over the trajectory."""
+    g = np.transpose(gold, (1, 2, 0))
+    scale = np.maximum(np.abs(g).max(axis=(0, 2), keepdims=True), 1e-3)
+    return (np.abs(u - g) / scale).max()
+
+
+@pytest.mark.parametrize("alg", ["tsit5", "rodas5p"])
+def test_pendulum_against_dop853_golden(oracle, alg):
+    gold = np.load(os.path.join(GOLD, "pendulum_dop853.npz"))
+    spec = ensembles.make_ensemble("C1", 1024)
+    r = _solve(oracle, spec, gold["index"], alg=alg)
+    assert (r["retcode"] == 1).all()
+    # global error vs the exact solution over 10 s of large swings (some released next to the
+    # inverted position phi = pi/2): bounded at the config's tolerance, and it converges
+    e8 = _scaled_err(r["u"], gold["u"])
+    r = _solve(oracle, spec, gold["index"], alg=alg, abstol=1e-12, reltol=1e-12)
+    e12 = _scaled_err(r["u"], gold["u"])
+    print(alg, "global error vs DOP853 golden: tol 1e-8 ->", e8, " tol 1e-12 ->", e12)
+    assert e8 < 2e-4 and e12 < 1e-7
+
+
+def test_spring_damper_against_closed_form_golden(oracle):
+    gold = np.load(os.path.join(GOLD, "spring_damper_dop853.npz"))
+    spec = ensembles.make_ensemble("C2", 6)
+    r = _solve(oracle, spec)
+    assert (r["retcode"] == 1).all()
+    assert _scaled_err(r["u"], gold["u"]) < 1e-6
+    # r_cm = 0: the line force produces no torque, the Euler angles of body1 stay at rest
+    assert np.abs(r["u"][:, 6:12, :]).max() < 1e-12
+
+
+def test_robot_against_radau_golden(oracle):
+    gold = np.load(os.path.join(GOLD, "robot6dof_radau.npz"))
+    for k, i in enumerate(gold["index"]):
+        spec = ensembles.make_ensemble("C4", 1, offset=int(i))
+        r = _solve(oracle, spec)
+        assert r["retcode"][0] == 1
+        assert _scaled_err(r["u"], gold["u"][k:k + 1]) < 1e-6
+
+
+def test_robot_forward_difference_jacobian_mode_agrees(oracle):
+    """`Rodas5P(autodiff=false)` (test/test_robot.jl:288) uses finite-difference J; a W-method
+    tolerates the difference: same trajectory within the north-star tolerance."""
+    spec = ensembles.make_ensemble("C4", 2)
+    a = _solve(oracle, spec)
+    b = _solve(oracle, spec, jac_mode=1)
+    scale = np.maximum(np.abs(a["u"]).max(axis=(0, 2), keepdims=True), 1e-3)
+    assert (np.abs(a["u"] - b["u"]) / scale).max() < 1e-6
+
+
+@pytest.mark.parametrize("alg,order", [("tsit5", 5), ("rodas5p", 5)])
+def test_fixed_step_convergence_order(oracle, alg, order):
+    spec = ensembles.make_ensemble("C1", 1024)
+    gold = np.load(os.path.join(GOLD, "pendulum_dop853.npz"))
+    i = int(gold["index"][2])
+    errs = []
+    hs = [0.05, 0.025, 0.0125]
+    for h in hs:
+        sv = np.array([2.0])
+        sysm = get_model("pendulum")
+        r = oracle.solve("pendulum", alg, spec.u0[:, [i]], spec.p[:, [i]], sysm.tables.pack(), (0.0, 2.0), sv,
+                         abstol=1e10, reltol=1e10, dt0=h, dtmax=h)
+        errs.append(np.abs(r["u"][0, :, 0] - gold["u"][2, 20]).max())
+    rates = np.log2(np.array(errs[:-1]) / np.array(errs[1:]))
+    assert rates.min() > order - 0.6, (errs, rates)
+
+
+def test_dense_output_matches_stepping_to_the_point(oracle):
+    """saveat comes from the dense output of the bracketing step (steps are not shortened)."""
+    spec = ensembles.make_ensemble("C4", 1)
+    sysm = get_model("robot6dof")
+    tb = sysm.tables.pack()
+    a = oracle.solve("robot6dof", "rodas5p", spec.u0, spec.p, tb, (0.0, 0.5), np.array([0.137, 0.3, 0.5]), abstol=1e-9, reltol=1e-9)
+    for j, te in enumerate([0.137, 0.3]):
+        b = oracle.solve("robot6dof", "rodas5p", spec.u0, spec.p, tb, (0.0, te), np.array([te]), abstol=1e-9, reltol=1e-9)
+        scale = np.maximum(np.abs(b["u"][0, :, 0]), 1e-2)
+        assert (np.abs(a["u"][j, :, 0] - b["u"][0, :, 0]) / scale).max() < 2e-6
+
+
+def test_reference_known_answers_pendulum(oracle):
+    sysm = get_model("pendulum")
+    tb = sysm.tables.pack()
+    sv = np.linspace(0, 10, 1001)
+    u0 = np.zeros((2, 1)); p = sysm.p0[:, None].copy()
+    r = oracle.solve("pendulum", "rodas5p", u0, p, tb, (0.0, 10.0), sv)          # defaults, like Rodas4() in the test
+    phi = r["u"][:, 0, 0]
+    k = KA["pendulum_phi_range"]
+    assert abs(phi.min() - k["min"]) < k["rtol"] * np.pi and abs(phi.max() - k["max"]) < k["atol"]
+    # damper d = 10: power sensor at t = 1 (test/basic_tests.jl:110-118); power = -d w^2
+    p[sysm.param_index("damper.d")] = 10.0
+    r = oracle.solve("pendulum", "rodas5p", u0, p, tb, (0.0, 1.0), np.array([1.0]))
+    w = r["u"][0, 1, 0]
+    assert abs(-10.0 * w * w - KA["pendulum_damper_power_t1_d10"]["value"]) < KA["pendulum_damper_power_t1_d10"]["atol"]
+    # damped pendulum settles at -pi/2 (test/basic_tests.jl:201)
+    p[sysm.param_index("damper.d")] = 0.5
+    r = oracle.solve("pendulum", "rodas5p", u0, p, tb, (0.0, 100.0), np.array([100.0]))
+    assert abs(r["u"][0, 0, 0] + np.pi / 2) < 1e-2 * np.pi / 2
+
+
+def test_reference_known_answers_robot(oracle):
+    """test/test_robot.jl:289,320-325: success; axis-1 tracking error < 0.01 on 0:0.1:2, at the
+    reference's default tolerances.  angle = joint angle; angle_ref = the PTP path."""
+    sysm = get_model("robot6dof")
+    tb = sysm.tables.pack()
+    sv = np.linspace(0, 2, 21)
+    r = oracle.solve("robot6dof", "rodas5p", sysm.u0[:, None], sysm.p0[:, None], tb, (0.0, 2.0), sv, jac_mode=1)
+    assert r["retcode"][0] == 1
+    # axisControlBus.angle = motor angle / ratio (src/robot/robot_components.jl:134,181)
+    q_ref = np.array([sysm.tables.eval("cubic", 0, 0, t) for t in sv])
+    assert np.abs(q_ref).max() > 0
+    angle = r["u"][:, sysm.state_index("axis1.motor.Jmotor.phi"), 0] / (-105.0)
+    err = np.abs(q_ref - angle)
+    print("axis-1 control error max", err.max())
+    assert err.max() < KA["robot_axis1_tracking_error"]["bound"]
+    np.testing.assert_allclose(r["u"][-1, 0:12:2, 0], np.deg2rad(KA["robot_q1_deg"]), atol=1e-2)
+
+
+def test_robot_rhs_equals_independent_newton_euler(oracle):
+    from ref_models import robot_rhs
+    sysm = get_model("robot6dof")
+    tb = sysm.tables.pack()
+    rng = np.random.default_rng(5)
+    for _ in range(6):
+        u = sysm.u0 + rng.normal(size=36) * np.where(np.arange(36) < 12, 0.5, 1.0)
+        p = sysm.p0 * (1 + 0.3 * rng.uniform(-1, 1, size=sysm.m))
+        t = rng.uniform(0, 2)
+        q_ref = [sysm.tables.eval("cubic", a, 0, t) for a in range(6)]
+        qd_ref = [sysm.tables.eval("linear", 6 + a, 0, t) for a in range(6)]
+        got = oracle.eval_fn("robot6dof", 0, u, p, t, tb)
+        want = robot_rhs(u, p, q_ref, qd_ref)
+        np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-9 * np.abs(want).max())
+
+
+def test_failure_codes(oracle):
+    spec = ensembles.make_ensemble("C1", 4)
+    r = _solve(oracle, spec, maxiters=10)
+    assert (r["retcode"] == 4).all() and np.isnan(r["u"][-1]).all()
+    r = _solve(oracle, spec, dtmin=1.0)
+    assert (r["retcode"] == 5).all()
