@@ -36,6 +36,7 @@ def parse():
     ap.add_argument("--trajectories", type=int, default=0, help="per-GPU ensemble size (0 = the config's full size)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="trajectories in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="tuning runs only: skip the host-buffer leg (the line then has no e2e)")
     return ap.parse_args()
 
 
@@ -103,7 +104,7 @@ def run_reference(args):
     from multibody_jl_b200.mechanics.zoo import get_model
     mbo.build()
     cores = os.cpu_count() or 1
-    sample = args.cpu_sample or max(64, 16 * cores)
+    sample = args.cpu_sample or max(256, 128 * cores)
     spec = ensembles.make_ensemble(args.config, sample)
     tb = get_model(spec.model).tables.pack()
 
@@ -230,17 +231,18 @@ def main():
             r = torch.from_numpy(h_red).to(dev)
             dist.all_reduce(r)
             h_red[:] = r.cpu().numpy()
-    e2e_step()
+    if not args.no_e2e:
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(0 if args.no_e2e else args.steps):
         e2e_step()
     barrier()
     e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_val = world * N * args.steps / e2e_t.item()
-    same = bool(np.array_equal(h_rc.numpy(), rc))
+    e2e_val = None if args.no_e2e else world * N * args.steps / e2e_t.item()
+    same = None if args.no_e2e else bool(np.array_equal(h_rc.numpy(), rc))
     h2d = 8 * N * (n + m) + 8 * ns
     d2h = 8 * N * n * ns + N * (8 + 4 + 20) + 8 * (2 * ns * n + 1)
 
@@ -267,7 +269,7 @@ def main():
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import mbo
         cores = os.cpu_count() or 1
-        sample = args.cpu_sample or max(64, 16 * cores)
+        sample = args.cpu_sample or max(256, 256 * cores)
         cs = ensembles.make_ensemble(args.config, sample)
         t0 = time.perf_counter()
         r = mbo.solve(cs.model, cs.alg, cs.u0, cs.p, sys_.tables.pack(), cs.tspan, cs.saveat, abstol=cs.abstol,

@@ -28,6 +28,22 @@ class Printer:
         self.scheduled = scheduled
         self.input_fmt = input_fmt
         self.interp_fmt = interp_fmt
+        self._seg: Dict[int, str] = {}        # time node -> name of its table-segment variable
+        self._paired: Dict[int, int] = {}     # sin/cos node -> partner emitted in the same MB_SINCOS
+        self._emitted: set = set()
+
+    def _begin(self, order: Sequence[int]) -> None:
+        """Per-function state: table segments already located, sin/cos pairs of one argument."""
+        g = self.g
+        self._seg, self._paired, self._emitted = {}, {}, set()
+        by_arg: Dict[int, Dict[int, int]] = {}
+        for n in order:
+            if g.op[n] in (SIN, COS):
+                by_arg.setdefault(g.a[n], {})[g.op[n]] = n
+        for d in by_arg.values():
+            if len(d) == 2:
+                self._paired[d[SIN]] = d[COS]
+                self._paired[d[COS]] = d[SIN]
 
     def ref(self, n: int) -> str:
         g = self.g
@@ -48,7 +64,21 @@ class Printer:
         o = g.op[n]
         if o in (CONST, INPUT, NEG):
             return None
+        if n in self._emitted:            # second half of a sin/cos pair
+            return None
         a, b, c = g.a[n], g.b[n], g.c[n]
+        if o in (SIN, COS) and n in self._paired:
+            m = self._paired[n]
+            self._emitted.add(m)
+            sn, cn = (n, m) if o == SIN else (m, n)
+            return f"{indent}double x{sn}, x{cn}; MB_SINCOS({r(a)}, x{sn}, x{cn});"
+        if o == INTERP:
+            kind, table, deriv = g.payload[n]
+            pre = ""
+            if a not in self._seg:
+                self._seg[a] = f"sg{a}"
+                pre = f"{indent}const MB_SEG_T sg{a} = MB_SEG(tb, {r(a)});\n"
+            return (f"{pre}{indent}const double x{n} = MB_TAB_{kind.upper()}{deriv}(tb, {self._seg[a]}, {table});")
         if o in (ADD, SUB, MUL, DIV):
             e = f"{r(a)} {'+-*/'[o - ADD]} {r(b)}"
         elif o == SIN:
@@ -77,7 +107,9 @@ class Printer:
     def body(self, outs: Sequence[int], indent: str = "  ") -> List[str]:
         g = self.g
         lines: List[str] = []
-        for n in (g.schedule(outs) if self.scheduled else g.reachable(outs)):
+        order = g.schedule(outs) if self.scheduled else g.reachable(outs)
+        self._begin(order)
+        for n in order:
             ln = self._line(n, indent)
             if ln is not None:
                 lines.append(ln)
@@ -90,6 +122,7 @@ class Printer:
         follow the temporaries."""
         g = self.g
         lines = [signature + " {"]
+        self._begin(g.reachable([n for _, n in assigns]))
         if not self.scheduled:
             lines += self.body([n for _, n in assigns], indent)
             for lhs, n in assigns:

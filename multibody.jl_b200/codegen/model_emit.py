@@ -12,7 +12,8 @@ src/Multibody.jl:184); this module prints, per model `X`:
   mbm_X_factor(u,p,t,tb,c,LU)     W = c*M - J (c = 1/(gamma*h)) built and LU-factored
                                   in one straight-line pass, pivot sequence fixed at
                                   code-generation time
-  mbm_X_solve(LU,b)               in-place W^-1 b with those factors
+  mbm_X_solve(LU,c,p,b)           in-place W^-1 b with those factors (state-independent cheap
+                                  factors are recomputed from c and p instead of being stored)
 
 plus sizes, the sparsity pattern, the mass-matrix diagonal and the algorithmic
 flop counts of each function (BASELINE.md section 4 cost table).
@@ -33,7 +34,7 @@ from .emit import Printer, sparse_lu, lu_solve
 class ModelCode:
     """Everything the emitter derived from a ReducedSystem (also used by tests)."""
 
-    def __init__(self, sys, pivots: Optional[Sequence[Tuple[int, int]]] = None):
+    def __init__(self, sys, pivots: Optional[Sequence[Tuple[int, int]]] = None, recompute_limit: float = 12.0):
         self.sys = sys
         g: Graph = sys.g
         n = sys.n
@@ -65,17 +66,74 @@ class ModelCode:
                 W[(i, i)] = g.add(W.get((i, i), g.zero), c)
         self.W_pattern = sorted(W)
         order, invd, L, U = sparse_lu(g, W, n, pivots=pivots)
-        # LU storage: for each elimination step, [1/pivot, U row entries..., L column entries...]
+        # LU storage: for each elimination step, [1/pivot, U row entries..., L column entries...].
+        # Structural constants take no storage.  Entries that do not depend on the state or on
+        # time (the drive blocks of the robot are linear: their factors are functions of
+        # c = 1/(gamma h) and the parameters only) and are cheap are NOT stored either: the
+        # solve recomputes them from (c, p, stored slots).  The kernels are bound by
+        # thread-local memory traffic, not by the FP64 pipe, so a few extra flops per solve
+        # are cheaper than a slot that is written once and read by all 8 stage solves.
         self.lu_nodes: List[int] = []
         self.lu_slots: Dict[Tuple[str, int, int], int] = {}
-
         self.lu_const: Dict[Tuple[str, int, int], float] = {}
+        self.lu_recomp: Dict[Tuple[str, int, int], int] = {}
+        from .dag import INPUT, INTERP, ADD, SUB, MUL, NEG
+        dep_cache: Dict[int, bool] = {}
+
+        def state_dep(n: int) -> bool:
+            stack = [n]
+            while stack:
+                k = stack[-1]
+                if k in dep_cache:
+                    stack.pop(); continue
+                o = g.op[k]
+                if o == CONST:
+                    dep_cache[k] = False; stack.pop(); continue
+                if o == INPUT:
+                    dep_cache[k] = g.payload[k][0] not in ("c", "p"); stack.pop(); continue
+                if o == INTERP:
+                    dep_cache[k] = True; stack.pop(); continue
+                kids = [g.a[k]] + ([g.b[k]] if g.b[k] >= 0 else []) + ([g.c[k]] if g.c[k] >= 0 and o not in (INTERP,) else [])
+                todo = [q for q in kids if q not in dep_cache]
+                if todo:
+                    stack.extend(todo); continue
+                dep_cache[k] = any(dep_cache[q] for q in kids)
+                stack.pop()
+            return dep_cache[n]
+        stored_node: Dict[int, int] = {}          # node -> slot (first slot holding it)
+        cost_cache: Dict[int, float] = {}
+
+        def recomp_cost(n: int) -> float:
+            """ops needed to rebuild n from (c, p, constants, stored slots); inf if not allowed"""
+            if n in stored_node:
+                return 0.0
+            if n in cost_cache:
+                return cost_cache[n]
+            o = g.op[n]
+            if o == CONST or (o == INPUT and g.payload[n][0] in ("c", "p")):
+                v = 0.0
+            elif o in (ADD, SUB, MUL):
+                v = 1.0 + recomp_cost(g.a[n]) + recomp_cost(g.b[n])
+            elif o == NEG:
+                v = recomp_cost(g.a[n])
+            else:
+                v = float("inf")
+            cost_cache[n] = v
+            return v
 
         def slot(kind, k, idx, node):
-            if g.op[node] == CONST:          # structural constants take no storage
+            if g.op[node] == CONST:
                 self.lu_const[(kind, k, idx)] = g.val[node]
                 return
+            if recompute_limit > 0 and not state_dep(node) and recomp_cost(node) <= recompute_limit:
+                self.lu_recomp[(kind, k, idx)] = node
+                return
+            if node in stored_node:               # same value already stored: share the slot
+                self.lu_slots[(kind, k, idx)] = stored_node[node]
+                return
             self.lu_slots[(kind, k, idx)] = len(self.lu_nodes)
+            stored_node[node] = len(self.lu_nodes)
+            cost_cache.clear()
             self.lu_nodes.append(node)
         for step, (pr, pc) in enumerate(order):
             slot("d", step, 0, invd[step])
@@ -87,10 +145,31 @@ class ModelCode:
         # --- solve graph (separate, tiny) ------------------------------------------
         sg = Graph()
         self.solve_graph = sg
+        copy_memo: Dict[int, int] = {}
+
+        def copy(n: int) -> int:
+            if n in stored_node:
+                return sg.input("lu", stored_node[n])
+            if n in copy_memo:
+                return copy_memo[n]
+            o = g.op[n]
+            if o == CONST:
+                r = sg.const(g.val[n])
+            elif o == INPUT:
+                r = sg.input(*g.payload[n])
+            elif o == NEG:
+                r = sg.neg(copy(g.a[n]))
+            else:
+                x, y = copy(g.a[n]), copy(g.b[n])
+                r = {ADD: sg.add, SUB: sg.sub, MUL: sg.mul}[o](x, y)
+            copy_memo[n] = r
+            return r
 
         def lu_in(kind, k, idx):
             if (kind, k, idx) in self.lu_const:
                 return sg.const(self.lu_const[(kind, k, idx)])
+            if (kind, k, idx) in self.lu_recomp:
+                return copy(self.lu_recomp[(kind, k, idx)])
             return sg.input("lu", self.lu_slots[(kind, k, idx)])
         sL = {k: [(i, lu_in("l", k, i)) for i, _ in L[k]] for k in range(n)}
         sU = {k: [(j, lu_in("u", k, j)) for j, _ in U[k]] for k in range(n)}
@@ -179,8 +258,9 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(pr.function(f"MB_FN void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     out.append("")
-    spr = Printer(code.solve_graph, {"lu": "LU[{i}]", "b": "b{i}"})
-    sol_lines = [f"MB_FN void mbm_{X}_solve(const double* MB_RESTRICT LU, double* MB_RESTRICT b) {{"]
+    spr = Printer(code.solve_graph, {"lu": "LU[{i}]", "b": "b{i}", "c": "c", "p": "p[{i}]"})
+    sol_lines = [f"MB_FN void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "
+                 f"double* MB_RESTRICT b) {{"]
     for i in range(n):
         sol_lines.append(f"  const double b{i} = b[{i}];")
     sol_lines += spr.body(code.solve_out)

@@ -6,40 +6,55 @@
 // ---- shared time tables ---------------------------------------------------------------
 // Uniform-grid lookups of the reference's KinematicPTP interpolants
 // (/root/reference/src/robot/path_planning.jl:191-193: CubicSpline, LinearInterpolation,
-// both with ExtrapolationType.Constant).  Packed layout: tb[0]=t0, tb[1]=dt, tb[2]=nk,
-// then per table nk interleaved (value, z) pairs -- one 32-byte sector per lookup.
-template <int CUBIC, int DERIV>
-__device__ __forceinline__ double mb_interp(const double* __restrict__ tb, int table, double t) {
+// both with ExtrapolationType.Constant).  The model image carries (value, z) pairs per knot
+// (include/mbb200.h); mbb200_model_load converts them to the device layout used here:
+//   tb[0..7]  = t0, h, nk, ntab, 0...                       (64-byte header)
+//   then (nk + 1) interval rows x ntab tables x 4 coefficients c0..c3 of
+//   S(a) = c0 + a (c1 + a (c2 + a c3)),  a = t - t_i        (one 32-byte sector per lookup)
+// Row 0 is "before the first knot" and row nk "after the last" (constant extrapolation:
+// c1..c3 = 0).  All tables of one row are contiguous, and a right-hand side evaluates all its
+// lookups at one time point, so the segment is located once (MB_SEG) and shared.
+#define MB_TB_HEADER 8
+struct MbSeg {
+  const double* row;   // coefficients of this interval, all tables
+  double a;            // t - t_i
+};
+__device__ __forceinline__ MbSeg mb_seg(const double* __restrict__ tb, double t) {
   const double t0 = __ldg(tb), h = __ldg(tb + 1);
-  const int nk = (int)__ldg(tb + 2);
+  const int nk = (int)__ldg(tb + 2), ntab = (int)__ldg(tb + 3);
   const double x = (t - t0) / h;
-  const double* base = tb + 3 + (size_t)table * 2 * nk;
-  if (x <= 0.0) return DERIV == 0 ? __ldg(base) : 0.0;
-  if (x >= (double)(nk - 1)) return DERIV == 0 ? __ldg(base + 2 * (nk - 1)) : 0.0;
-  int i = (int)x;
+  int row, i = (int)x;
   if (i > nk - 2) i = nk - 2;
-  const double a = (x - i) * h, b = h - a;
-  const double v0 = __ldg(base + 2 * i), z0 = __ldg(base + 2 * i + 1);
-  const double v1 = __ldg(base + 2 * i + 2), z1 = __ldg(base + 2 * i + 3);
-  if (!CUBIC) {
-    if (DERIV == 0) return (v0 * b + v1 * a) / h;
-    return DERIV == 1 ? (v1 - v0) / h : 0.0;
-  }
-  const double c0 = v0 / h - z0 * h / 6.0, c1 = v1 / h - z1 * h / 6.0;
-  if (DERIV == 0) return z0 * b * b * b / (6 * h) + z1 * a * a * a / (6 * h) + c1 * a + c0 * b;
-  if (DERIV == 1) return -z0 * b * b / (2 * h) + z1 * a * a / (2 * h) + c1 - c0;
-  if (DERIV == 2) return (z0 * b + z1 * a) / h;
-  if (DERIV == 3) return (z1 - z0) / h;
+  if (x <= 0.0) { row = 0; i = 0; }
+  else if (x >= (double)(nk - 1)) row = nk;
+  else row = i + 1;
+  MbSeg sg;
+  sg.row = tb + MB_TB_HEADER + (size_t)row * ntab * 4;
+  sg.a = (x - i) * h;
+  return sg;
+}
+template <int DERIV>
+__device__ __forceinline__ double mb_tab(const MbSeg& sg, int table) {
+  const double2* c = reinterpret_cast<const double2*>(sg.row + table * 4);
+  const double2 c01 = __ldg(c), c23 = __ldg(c + 1);
+  const double a = sg.a;
+  if (DERIV == 0) return fma(a, fma(a, fma(a, c23.y, c23.x), c01.y), c01.x);
+  if (DERIV == 1) return fma(a, fma(a, 3.0 * c23.y, 2.0 * c23.x), c01.y);
+  if (DERIV == 2) return fma(a, 6.0 * c23.y, 2.0 * c23.x);
+  if (DERIV == 3) return 6.0 * c23.y;
   return 0.0;
 }
-#define mb_interp_cubic0(tb, k, t) mb_interp<1, 0>(tb, k, t)
-#define mb_interp_cubic1(tb, k, t) mb_interp<1, 1>(tb, k, t)
-#define mb_interp_cubic2(tb, k, t) mb_interp<1, 2>(tb, k, t)
-#define mb_interp_cubic3(tb, k, t) mb_interp<1, 3>(tb, k, t)
-#define mb_interp_linear0(tb, k, t) mb_interp<0, 0>(tb, k, t)
-#define mb_interp_linear1(tb, k, t) mb_interp<0, 1>(tb, k, t)
-#define mb_interp_linear2(tb, k, t) mb_interp<0, 2>(tb, k, t)
-#define mb_interp_linear3(tb, k, t) mb_interp<0, 3>(tb, k, t)
+#define MB_SEG_T MbSeg
+#define MB_SEG(tb, t) mb_seg(tb, t)
+#define MB_TAB_CUBIC0(tb, sg, k) mb_tab<0>(sg, k)
+#define MB_TAB_CUBIC1(tb, sg, k) mb_tab<1>(sg, k)
+#define MB_TAB_CUBIC2(tb, sg, k) mb_tab<2>(sg, k)
+#define MB_TAB_CUBIC3(tb, sg, k) mb_tab<3>(sg, k)
+#define MB_TAB_LINEAR0(tb, sg, k) mb_tab<0>(sg, k)
+#define MB_TAB_LINEAR1(tb, sg, k) mb_tab<1>(sg, k)
+#define MB_TAB_LINEAR2(tb, sg, k) mb_tab<2>(sg, k)
+#define MB_TAB_LINEAR3(tb, sg, k) mb_tab<3>(sg, k)
+#define MB_SINCOS(x, s, c) sincos(x, &(s), &(c))
 
 // ---- method coefficients (published methods) ------------------------
 // __constant__ tables: indices are warp-uniform, so every read is a constant-bank broadcast.

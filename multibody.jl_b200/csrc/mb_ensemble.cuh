@@ -171,7 +171,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
       double EEst;
       if (ROSEN) {
         // ---- Rodas5P step: W = M/(gamma dt) - J factored once, 8 stage solves ------------
-        M::factor(u, p, t, tb, 1.0 / (dt * RD_GAMMA), LU);
+        const double cW = 1.0 / (dt * RD_GAMMA);
+        M::factor(u, p, t, tb, cW, LU);
         njac++;
         if (M::HAS_DT) M::dT(u, p, t, tb, dT);
         const double inv_dt = 1.0 / dt;
@@ -200,7 +201,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
             if (M::isdiff(i)) v = fma(sc[i], inv_dt, v);
             r[i] = v;
           }
-          M::solve(LU, r);
+          M::solve(LU, cW, p, r);
 #pragma unroll
           for (int i = 0; i < N; i++) k[s][i] = r[i];
         }

@@ -4,6 +4,14 @@
 #pragma once
 #include "mb_ensemble.cuh"
 #include "mb_registry.h"
+#include <cstdlib>
+
+// tuning knob: MBB200_CTAS_PER_SM caps the resident CTAs per SM (persistent grid size)
+static inline int mb_cap_ctas_per_sm(int bps) {
+  const char* e = getenv("MBB200_CTAS_PER_SM");
+  const int cap = e ? atoi(e) : 0;
+  return (cap > 0 && cap < bps) ? cap : bps;
+}
 
 #define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
   struct MbModel_##X {                                                                              \
@@ -21,8 +29,9 @@
                                                   const double* tb, double c, double* LU) {         \
       mbm_##X##_factor(u, p, t, tb, c, LU);                                                         \
     }                                                                                               \
-    static __device__ __forceinline__ void solve(const double* LU, double* b) {                     \
-      mbm_##X##_solve(LU, b);                                                                       \
+    static __device__ __forceinline__ void solve(const double* LU, double c, const double* p,       \
+                                                 double* b) {                                       \
+      mbm_##X##_solve(LU, c, p, b);                                                                 \
     }                                                                                               \
     static __device__ __forceinline__ int isdiff(int i) { return mbm_##X##_isdiff(i); }             \
   };                                                                                                \
@@ -32,6 +41,7 @@
       auto kern = mbk::ensemble_kernel<MbModel_##X, 1, BLOCK, MINB, UNR>;                           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 0);                \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, 0);                          \
+      bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
       long long need = (a.N + BLOCK - 1) / BLOCK;                                                   \
       if (grid > need) grid = need;                                                                 \
@@ -40,6 +50,7 @@
       auto kern = mbk::ensemble_kernel<MbModel_##X, 2, BLOCK, MINB, UNR>;                           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 0);                \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, 0);                          \
+      bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
       long long need = (a.N + BLOCK - 1) / BLOCK;                                                   \
       if (grid > need) grid = need;                                                                 \

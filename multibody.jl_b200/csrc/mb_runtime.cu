@@ -156,12 +156,42 @@ extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** o
   if (!e) return fail(MBB200_ERR_UNKNOWN_MODEL, "no compiled kernel set for model '%s'", h.name);
   if (e->n != h.n || e->m != h.m)
     return fail(MBB200_ERR_BAD_ARG, "image of '%s' has n=%d m=%d, compiled model has n=%d m=%d", h.name, h.n, h.m, e->n, e->m);
-  if (h.n_table < 3 || len < sizeof(h) + (size_t)h.n_table * sizeof(double))
-    return fail(MBB200_ERR_BAD_ARG, "truncated table data");
   mbb200_model* m = new mbb200_model;
+  if (h.n_table < 3 || len < sizeof(h) + (size_t)h.n_table * sizeof(double))
+  {
+    delete m;
+    return fail(MBB200_ERR_BAD_ARG, "truncated table data");
+  }
   m->entry = e;
-  m->tables.resize(h.n_table);
-  std::memcpy(m->tables.data(), (const char*)image + sizeof(h), (size_t)h.n_table * sizeof(double));
+  {
+    // image tables: [t0, h, nk] + per table nk (value, z) pairs -> device layout of
+    // mb_common.cuh: 8-double header + (nk + 1) interval rows x ntab x 4 polynomial coefficients
+    std::vector<double> img(h.n_table);
+    std::memcpy(img.data(), (const char*)image + sizeof(h), (size_t)h.n_table * sizeof(double));
+    const double t0 = img[0], hh = img[1];
+    const long long nk = (long long)img[2];
+    const long long ntab = nk > 0 ? ((long long)h.n_table - 3) / (2 * nk) : 0;
+    if (nk < 0 || (nk > 0 && (nk < 2 || !(hh > 0.0) || 3 + 2 * nk * ntab != (long long)h.n_table))) {
+      delete m;
+      return fail(MBB200_ERR_BAD_ARG, "inconsistent table block (nk=%lld, n_table=%lld)", nk, (long long)h.n_table);
+    }
+    m->tables.assign(MB_TB_HEADER + (size_t)(nk + 1) * ntab * 4, 0.0);
+    m->tables[0] = t0; m->tables[1] = hh > 0.0 ? hh : 1.0; m->tables[2] = (double)nk; m->tables[3] = (double)ntab;
+    for (long long k = 0; k < ntab; k++) {
+      const double* T = img.data() + 3 + (size_t)k * 2 * nk;
+      for (long long row = 0; row <= nk; row++) {
+        double* c = m->tables.data() + MB_TB_HEADER + ((size_t)row * ntab + k) * 4;
+        if (row == 0) { c[0] = T[0]; continue; }
+        if (row == nk) { c[0] = T[2 * (nk - 1)]; continue; }
+        const long long i = row - 1;
+        const double v0 = T[2 * i], z0 = T[2 * i + 1], v1 = T[2 * i + 2], z1 = T[2 * i + 3];
+        c[0] = v0;
+        c[1] = (v1 - v0) / hh - hh * (2.0 * z0 + z1) / 6.0;
+        c[2] = 0.5 * z0;
+        c[3] = (z1 - z0) / (6.0 * hh);
+      }
+    }
+  }
   m->d_tables.assign(g_dev.size(), nullptr);
   for (size_t i = 0; i < g_dev.size(); i++) {
     cudaError_t ce = cudaSetDevice(g_dev[i].ordinal);

@@ -23,7 +23,7 @@ typedef struct {
   mbo_fn rhs, jac, dT;
   int nlu;            /* slots of the product's generated structured LU (checked in tests only) */
   void (*factor)(const double* u, const double* p, double t, const double* tb, double c, double* LU);
-  void (*solve)(const double* LU, double* b);
+  void (*solve)(const double* LU, double c, const double* p, double* b);
 } mbo_model;
 
 const mbo_model* mbo_find_model(const char* name);

@@ -38,4 +38,18 @@ static inline double mbo_interp(const double* tb, int table, double t, int cubic
 #define mb_interp_linear1(tb, k, t) mbo_interp(tb, k, t, 0, 1)
 #define mb_interp_linear2(tb, k, t) mbo_interp(tb, k, t, 0, 2)
 #define mb_interp_linear3(tb, k, t) mbo_interp(tb, k, t, 0, 3)
+/* generated-header hooks: the oracle locates the segment per lookup and evaluates the
+ * DataInterpolations formulas above (the product shares the segment and uses the expanded
+ * polynomial, csrc/mb_common.cuh) */
+#define MB_SEG_T double
+#define MB_SEG(tb, t) (t)
+#define MB_TAB_CUBIC0(tb, sg, k) mbo_interp(tb, k, sg, 1, 0)
+#define MB_TAB_CUBIC1(tb, sg, k) mbo_interp(tb, k, sg, 1, 1)
+#define MB_TAB_CUBIC2(tb, sg, k) mbo_interp(tb, k, sg, 1, 2)
+#define MB_TAB_CUBIC3(tb, sg, k) mbo_interp(tb, k, sg, 1, 3)
+#define MB_TAB_LINEAR0(tb, sg, k) mbo_interp(tb, k, sg, 0, 0)
+#define MB_TAB_LINEAR1(tb, sg, k) mbo_interp(tb, k, sg, 0, 1)
+#define MB_TAB_LINEAR2(tb, sg, k) mbo_interp(tb, k, sg, 0, 2)
+#define MB_TAB_LINEAR3(tb, sg, k) mbo_interp(tb, k, sg, 0, 3)
+#define MB_SINCOS(x, s, c) do { (s) = sin(x); (c) = cos(x); } while (0)
 #endif

@@ -62,7 +62,7 @@ int mbo_factor_solve(const char* name, const double* u, const double* p, double 
   if (!md) return -1;
   double* LU = (double*)calloc(md->nlu > 0 ? md->nlu : 1, sizeof(double));
   md->factor(u, p, t, tb, c, LU);
-  md->solve(LU, b);
+  md->solve(LU, c, p, b);
   free(LU);
   return 0;
 }
