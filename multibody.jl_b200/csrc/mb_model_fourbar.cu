@@ -1,0 +1,7 @@
+// Kernel set of model 'fourbar' (C3: closed loop, index-1 mass-matrix DAE; Rodas5P only).
+#include "mb_model_def.cuh"
+#define MB_FN static __device__ __forceinline__
+#define MB_RESTRICT __restrict__
+#define MB_NO_PATTERN
+#include "generated/mbm_fourbar.h"
+MB_DEFINE_MODEL(fourbar, 128, 1, 0)

@@ -55,11 +55,14 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C2":    # spring-damper, 1M parameter sets, Tsit5, 100 saves (spring_damper_system.md:21-63)
         total, model, alg, tol = 1 << 20, "spring_damper", "tsit5", 1e-8
         saveat = 0.05 * np.arange(1, 101)
+    elif config == "C3":    # fourbar closed loop, 256k crank speeds, Rodas5P (test/test_fourbar.jl:13-46)
+        total, model, alg, tol = 1 << 18, "fourbar", "rodas5p", 1e-8
+        saveat = np.linspace(0.0, 1.4399, 21)[1:]
     elif config == "C4":    # Robot6DOF parameter sweep, 1M, Rodas5P reltol 1e-8 (test/test_robot.jl:268-288)
         total, model, alg, tol = 1 << 20, "robot6dof", "rodas5p", 1e-8
         saveat = np.linspace(0.0, 2.0, 21)
     else:
-        raise KeyError(f"config {config} is not built yet (C1, C2, C4 are)")
+        raise KeyError(f"config {config} is not built yet (C1, C2, C3, C4 are)")
     N = total if N is None else int(N)
     sys = get_model(model)
     idx = np.arange(offset, offset + N, dtype=np.int64)
@@ -76,6 +79,8 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
         P[sys.param_index("damper1.d")] = d
         P[sys.param_index("body1.m")] = m
         P[sys.param_index("body2.m")] = m
+    elif config == "C3":
+        U[sys.state_index("j1.w")] = uniform(idx, 0, 3.0, 7.0)
     elif config == "C4":
         P[sys.param_index("mechanics.load.m")] = uniform(idx, 0, 5.0, 25.0)
         for a in range(6):

@@ -13,6 +13,7 @@ import numpy as np
 from .builder import ModelBuilder, ReducedSystem
 from .mechanism import Mechanism
 from .robot import robot6dof
+from .loops import LoopMechanism
 
 
 def pendulum() -> ReducedSystem:
@@ -66,10 +67,92 @@ def spring_damper() -> ReducedSystem:
     return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
 
 
+def consistent_positions(sysm_g, closure, q_nodes, q0, dep, iters: int = 50, tol: float = 1e-14):
+    """Newton on the closure conditions g(q) = 0 for the dependent coordinates (the
+    reference leaves this to MTK's initialisation problem, test/test_fourbar.jl:44,70)."""
+    g = sysm_g
+    q = np.array(q0, dtype=float)
+    J = g.diff(closure, [q_nodes[k] for k in dep])
+    jn = [[J[i].get(j, g.zero) for j in range(len(dep))] for i in range(len(closure))]
+    flat = [n for row in jn for n in row]
+    for _ in range(iters):
+        inp = {g.payload[qn]: float(v) for qn, v in zip(q_nodes, q)}
+        vals = g.evaluate(list(closure) + flat, inp, None)
+        r = np.array(vals[:len(closure)])
+        A = np.array(vals[len(closure):]).reshape(len(closure), len(dep))
+        if np.abs(r).max() < tol:
+            break
+        q[dep] -= np.linalg.solve(A, r)
+    else:
+        raise RuntimeError("closure Newton iteration did not converge")
+    return q
+
+
+def fourbar() -> ReducedSystem:
+    """C3. Spatial four-bar with a prismatic leg and a cut revolute joint
+    (test/test_fourbar.jl:13-42; docs/src/examples/kinematic_loops.md:90-150).
+    Branch A: world -> j1 (x) -> b1 -> j3 (x) -> j4 (y) -> [j5 cut, z];
+    branch B: world -> b0 [1.2,0,0] -> j2 Prismatic (x) -> b2 -> rev (y) -> rev1 (z) -> b3 -> [j5].
+    States: j1.phi, j1.w differential (state_priority = 10 in the reference); the five other
+    tree coordinates algebraic.  n = 7 (the reference reports 8: MTK keeps one more
+    algebraic unknown; the cut angle j5.phi is eliminated here)."""
+    mb = ModelBuilder("fourbar")
+    mech = LoopMechanism(mb)
+    phi1 = mb.state("j1.phi", 0.0)
+    w1 = mb.state("j1.w", 5.235987755982989)
+    s2 = mb.state("j2.s", -0.2, differential=False)
+    q_rev = mb.state("rev.phi", 0.0, differential=False)
+    q_rev1 = mb.state("rev1.phi", 0.0, differential=False)
+    q3 = mb.state("j3.phi", 0.0, differential=False)
+    q4 = mb.state("j4.phi", 0.0, differential=False)
+    deps = [s2, q_rev, q_rev1, q3, q4]
+    vd = {q.n: mech.dependent_velocity(q) for q in deps}
+    world = mech.world()
+    # joints are created in the order of q_all below
+    j1 = mech.revolute(world, (1, 0, 0), phi1, w1, name="j1")
+    b0 = mech.fixed_translation(world, (1.2, 0.0, 0.0))
+    j2 = mech.prismatic(b0, (1, 0, 0), s2, vd[s2.n], name="j2")
+    b2 = mech.body_shape(j2, (0.0, 0.2, 0.0), 1.0)
+    rev = mech.revolute(b2, (0, 1, 0), q_rev, vd[q_rev.n], name="rev")
+    rev1 = mech.revolute(rev, (0, 0, 1), q_rev1, vd[q_rev1.n], name="rev1")
+    b3 = mech.body_shape(rev1, (-1.0, 0.3, 0.1), 1.0)
+    b1 = mech.body_shape(j1, (0.0, 0.5, 0.1), 1.0)
+    j3 = mech.revolute(b1, (1, 0, 0), q3, vd[q3.n], name="j3")
+    j4 = mech.revolute(j3, (0, 1, 0), q4, vd[q4.n], name="j4")
+    mech.cut_revolute(j4, b3, (0, 0, 1))
+    q_all = [phi1, s2, q_rev, q_rev1, q3, q4]
+    v_all = [w1] + [vd[q.n] for q in deps]
+    mech.solve_loops(q_all, v_all)
+    q0 = consistent_positions(mb.g, mech.closure, [q.n for q in q_all], [mb.u0[mb.index_of(q)] for q in q_all],
+                              mech.dep)
+    for q, v in zip(q_all, q0):
+        mb.u0[mb.index_of(q)] = float(v)
+    sysm = mb.finish(tspan=(0.0, 1.4399), mechanism=mech)
+    sysm.meta["pivots"] = static_pivots(sysm)
+    return sysm
+
+
+def static_pivots(sysm: ReducedSystem, h: float = 1e-3):
+    """Pivot sequence of the generated sparse LU of W = M/(gamma h) - J for systems whose
+    algebraic rows have no usable diagonal: threshold-Markowitz on a numeric sample at u0
+    (Jacobian by central differences of the interpreted RHS)."""
+    from ..codegen.emit import choose_pivots_numeric
+    n = sysm.n
+    J = np.zeros((n, n))
+    for j in range(n):
+        e = np.zeros(n)
+        e[j] = 1e-6
+        J[:, j] = (sysm.eval_rhs(sysm.u0 + e, sysm.p0, 0.0) - sysm.eval_rhs(sysm.u0 - e, sysm.p0, 0.0)) / 2e-6
+    W = np.diag(sysm.mass_diag.astype(float)) / (0.21193756319429014 * h) - J
+    W[np.abs(W) < 1e-8 * np.abs(W).max()] = 0.0
+    return choose_pivots_numeric(W)
+
+
 MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "pendulum": pendulum,
     "spring_damper": spring_damper,
     "robot6dof": robot6dof,
+    "fourbar": fourbar,
 }
 _cache: Dict[str, ReducedSystem] = {}
 

@@ -8,6 +8,8 @@ container; scipy is the independent integrator):
  * spring_damper_dop853.npz C2 parameter sets, closed-form point-mass equations derived by
                             hand from docs/src/examples/spring_damper_system.md:21-61
  * robot6dof_radau.npz      C4 parameter sets, generated RHS/Jacobian, scipy Radau rtol=1e-10
+ * fourbar_lagrange.npz      C3 crank speeds, independent 1-DOF Lagrange derivation (numpy forward
+                            kinematics + Newton closure), scipy DOP853 rtol=1e-7
  * reference_known_answers.json  numbers asserted by the reference's own tests (Appendix D)
 The Julia reference cannot run here, so these pin the oracle's *integrators* against an
 independent implementation and its *models* against hand-derived closed forms.
@@ -91,6 +93,97 @@ def robot():
     np.savez(os.path.join(HERE, "robot6dof_radau.npz"), index=idx, saveat=spec.saveat, u=np.array(out))
 
 
+def _rot(axis, a):
+    c, s_ = np.cos(a), np.sin(a)
+    if axis == 0:
+        return np.array([[1, 0, 0], [0, c, -s_], [0, s_, c]])
+    if axis == 1:
+        return np.array([[c, 0, s_], [0, 1, 0], [-s_, 0, c]])
+    return np.array([[c, -s_, 0], [s_, c, 0], [0, 0, 1]])
+
+
+class FourbarLagrange:
+    """Independent 1-DOF derivation of the four-bar of test/test_fourbar.jl:13-42: closure
+    solved by Newton for q_D(phi), then  m_red(phi) phi'' + m_red'(phi) phi'^2 / 2 + V'(phi) = 0
+    with m_red, V from plain forward kinematics and nested central differences."""
+
+    def __init__(self):
+        self.qd = np.array([-0.2, 0.0, 0.0, 0.0, 0.0])      # s, rev, rev1, j3, j4
+
+    @staticmethod
+    def fk(phi, qd):
+        s, a_rev, a_rev1, a3, a4 = qd
+        R1 = _rot(0, phi)
+        p2 = np.array([1.2 + s, 0.0, 0.0])
+        p3 = p2 + np.array([0.0, 0.2, 0.0])
+        T3 = _rot(1, a_rev) @ _rot(2, a_rev1)
+        TA = R1 @ _rot(0, a3) @ _rot(1, a4)
+        pA = R1 @ np.array([0.0, 0.5, 0.1])
+        pB = p3 + T3 @ np.array([-1.0, 0.3, 0.1])
+        nb = TA.T @ T3 @ np.array([0.0, 0.0, 1.0])
+        g = np.concatenate([pB - pA, nb[:2]])
+        coms = [R1 @ np.array([0.0, 0.25, 0.05]), p2 + np.array([0.0, 0.1, 0.0]), p3 + T3 @ np.array([-0.5, 0.15, 0.05])]
+        return g, coms, [R1, np.eye(3), T3]
+
+    def solve_qd(self, phi, guess=None):
+        qd = np.array(self.qd if guess is None else guess, dtype=float)
+        for _ in range(60):
+            g = self.fk(phi, qd)[0]
+            if np.abs(g).max() < 1e-14:
+                break
+            J = np.zeros((5, 5))
+            for j in range(5):
+                e = np.zeros(5); e[j] = 1e-7
+                J[:, j] = (self.fk(phi, qd + e)[0] - self.fk(phi, qd - e)[0]) / 2e-7
+            qd = qd - np.linalg.solve(J, g)
+        return qd
+
+    def energy_terms(self, phi):
+        """(m_red, V) at phi."""
+        h = 1e-5
+        q0 = self.solve_qd(phi)
+        self.qd = q0
+        qp, qm = self.solve_qd(phi + h, q0), self.solve_qd(phi - h, q0)
+        _, c0, T0 = self.fk(phi, q0)
+        _, cp, Tp = self.fk(phi + h, qp)
+        _, cm, Tm = self.fk(phi - h, qm)
+        mred = 0.0
+        for k in range(3):
+            dr = (cp[k] - cm[k]) / (2 * h)
+            Wm = ((Tp[k] - Tm[k]) / (2 * h)) @ T0[k].T
+            w = np.array([Wm[2, 1], Wm[0, 2], Wm[1, 0]])
+            mred += 1.0 * dr @ dr + 0.001 * w @ w
+        V = sum(1.0 * G * c[1] for c in c0)
+        return mred, V
+
+    def rhs(self, t, y):
+        phi, w = y
+        h = 1e-4
+        m0, _ = self.energy_terms(phi)
+        mp, Vp = self.energy_terms(phi + h)
+        mm, Vm = self.energy_terms(phi - h)
+        self.energy_terms(phi)          # leave the Newton guess at phi
+        return [w, -(0.5 * (mp - mm) / (2 * h) * w * w + (Vp - Vm) / (2 * h)) / m0]
+
+
+def fourbar():
+    w0s = np.array([5.235987755982989, 3.0, 6.5])
+    sv = np.linspace(0.0, 1.4399, 21)[1:]
+    out = []
+    for w0 in w0s:
+        fb = FourbarLagrange()
+        r = solve_ivp(fb.rhs, (0.0, 1.4399), [0.0, w0], method="DOP853", rtol=1e-7, atol=1e-9, t_eval=sv)   # the nested differences carry ~1e-7 noise
+        fb2 = FourbarLagrange()
+        rows = []
+        for k in range(len(sv)):
+            qd = fb2.solve_qd(r.y[0, k])
+            fb2.qd = qd
+            rows.append(np.concatenate([r.y[:, k], qd]))
+        out.append(np.array(rows))
+        print("fourbar", w0, r.nfev, rows[-1])
+    np.savez(os.path.join(HERE, "fourbar_lagrange.npz"), w0=w0s, saveat=sv, u=np.array(out))
+
+
 def known_answers():
     ka = {
         "pendulum_phi_range": {"min": -np.pi, "max": 0.0, "rtol": 1e-2, "atol": 1e-2, "src": "test/basic_tests.jl:104-105"},
@@ -104,6 +197,11 @@ def known_answers():
 
 
 if __name__ == "__main__":
+    if len(sys.argv) > 1:
+        for name in sys.argv[1:]:
+            globals()[name]()
+        sys.exit(0)
+    fourbar()
     pendulum()
     spring_damper()
     robot()

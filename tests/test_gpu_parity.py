@@ -42,7 +42,7 @@ def _compare(sol, ref, rtol=RTOL):
     assert abs(ga.mean() - oa.mean()) <= 0.02 * oa.mean() + 2
 
 
-@pytest.mark.parametrize("config,N", [("C1", 1024), ("C2", 2048), ("C4", 256)])
+@pytest.mark.parametrize("config,N", [("C1", 1024), ("C2", 2048), ("C3", 1024), ("C4", 256)])
 def test_config_parity(oracle, config, N):
     spec = ensembles.make_ensemble(config, N)
     _compare(_run_gpu(spec), _run_oracle(oracle, spec))
@@ -73,6 +73,30 @@ def test_failed_trajectories_do_not_fail_the_call(oracle):
                        spec.saveat, abstol=1e-8, reltol=1e-8, maxiters=10)
     assert np.array_equal(sol.retcode, ref["retcode"])
     np.testing.assert_allclose(sol.t_final, ref["t"], rtol=1e-6)   # step sizes differ at rounding level (FMA contraction)
+
+
+def test_tsit5_refuses_a_dae():
+    from multibody_jl_b200 import _lib
+    spec = ensembles.make_ensemble("C3", 8)
+    spec.alg = "tsit5"
+    with pytest.raises(_lib.Mbb200Error, match="singular mass matrix"):
+        _run_gpu(spec)
+
+
+def test_fourbar_loop_stays_closed_at_scale():
+    """Size-independent property of C3: closure residuals of every saved state are ~0."""
+    spec = ensembles.make_ensemble("C3", 8192, offset=100000)
+    sol = _run_gpu(spec)
+    assert np.all(sol.retcode == 1)
+    q = sol.u[-1]                       # [n][N] at t1
+    # closure: frame positions of both branches coincide (numpy forward kinematics)
+    phi, s_, a3 = q[0], q[2], q[5]
+    pA = np.stack([np.zeros_like(phi), 0.5 * np.cos(phi) - 0.1 * np.sin(phi), 0.5 * np.sin(phi) + 0.1 * np.cos(phi)])
+    cr, sr, c1, s1 = np.cos(q[3]), np.sin(q[3]), np.cos(q[4]), np.sin(q[4])
+    r3 = np.array([-1.0, 0.3, 0.1])
+    v = np.stack([c1 * r3[0] - s1 * r3[1], s1 * r3[0] + c1 * r3[1], np.full_like(phi, r3[2])])     # Rot_z(rev1) r3
+    pB = np.stack([1.2 + s_ + cr * v[0] + sr * v[2], 0.2 + v[1], -sr * v[0] + cr * v[2]])          # Rot_y(rev) ...
+    assert np.abs(pA - pB).max() < 1e-6
 
 
 def test_reduction_matches_host_statistics():

@@ -66,6 +66,31 @@ def test_robot_against_radau_golden(oracle):
         assert _scaled_err(r["u"], gold["u"][k:k + 1]) < 1e-6
 
 
+def test_fourbar_against_independent_lagrange_golden(oracle):
+    """C3 (test/test_fourbar.jl:13-46): the index-1 DAE from mechanics/loops.py vs a 1-DOF
+    Lagrange derivation with numpy forward kinematics (tests/golden/make_golden.py).  The golden
+    carries ~1e-5 of finite-difference noise; a modelling error would be O(1)."""
+    gold = np.load(os.path.join(GOLD, "fourbar_lagrange.npz"))
+    sysm = get_model("fourbar")
+    assert list(sysm.mass_diag) == [1, 1, 0, 0, 0, 0, 0]       # 2 differential states (kinematic_loops.md:113)
+    for k, w0 in enumerate(gold["w0"]):
+        u0 = sysm.u0.copy()
+        u0[sysm.state_index("j1.w")] = w0
+        r = oracle.solve("fourbar", "rodas5p", u0[:, None], np.zeros((1, 1)), sysm.tables.pack(), (0.0, 1.4399),
+                         gold["saveat"], abstol=1e-9, reltol=1e-9)
+        assert r["retcode"][0] == 1                                  # test/test_fourbar.jl:46
+        assert np.abs(r["u"][:, :, 0] - gold["u"][k]).max() < 2e-4
+        # loop stays closed: algebraic residuals at the saved (interpolated) points
+        for j in (0, 7, 19):
+            assert np.abs(sysm.eval_rhs(r["u"][j, :, 0], sysm.p0, 0.0)[2:]).max() < 1e-7
+
+
+def test_fourbar_initial_configuration_is_consistent():
+    sysm = get_model("fourbar")
+    assert np.abs(sysm.eval_rhs(sysm.u0, sysm.p0, 0.0)[2:]).max() < 1e-13
+    assert sysm.u0[sysm.state_index("j2.s")] == pytest.approx(-0.2)   # the reference's s guess is already consistent
+
+
 def test_robot_forward_difference_jacobian_mode_agrees(oracle):
     """`Rodas5P(autodiff=false)` (test/test_robot.jl:288) uses finite-difference J; a W-method
     tolerates the difference: same trajectory within the north-star tolerance."""
