@@ -22,7 +22,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
-METRIC = "ensemble trajectories/sec (Robot6DOF Rodas5P)"
+METRIC = "ensemble trajectories/sec (Robot6DOF Rodas5P)"      # BASELINE.json metric (config C4)
+
+
+def metric_name(spec):
+    return METRIC if spec.config == "C4" else f"ensemble trajectories/sec ({spec.model} {spec.alg})"
 UNIT = "trajectories/s"
 
 
@@ -80,10 +84,15 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": reasons}
 
 
-def flops_per_trajectory(flops, n, n_save, stats):
+def flops_per_trajectory(flops, n, n_save, stats, alg="rodas5p"):
     """Algorithmic FLOPs (BASELINE.md section 4 / SURVEY.md 8d), from the measured step counts.
-    Rodas5P: F_step = F_factor(jac + structured LU) + F_dT + 8 F_rhs + 8 F_solve + 86 n + 4 n."""
+    Rodas5P: F_step = F_factor(jac + structured LU) + F_dT + 8 F_rhs + 8 F_solve + 86 n + 4 n.
+    Tsit5:   F_step = 6 F_rhs + 56 n (the two are equal: no linear algebra)."""
     steps = stats[0].astype(np.float64) + stats[1].astype(np.float64)
+    if alg == "tsit5":
+        f_step = dense_step = 6 * flops["rhs"] + 56 * n
+        f_interp = (7 * 2 + 7 * 8 + 2) * n
+        return steps * f_step + n_save * f_interp + 3 * flops["rhs"], f_step, dense_step, steps
     f_step = flops["factor"] + flops["dT"] + 8 * flops["rhs"] + 8 * flops["solve"] + 86 * n + 4 * n
     f_interp = (8 * 3 * 2 + 10) * n
     dense_step = flops["jac"] + flops["dT"] + (2 * n ** 3) // 3 + 8 * flops["rhs"] + 16 * n * n + 86 * n + 4 * n
@@ -120,7 +129,7 @@ def run_reference(args):
     v = sample * args.steps / dt
     full = spec.n_total if not args.trajectories else args.trajectories
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": metric_name(spec), "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(spec, full), "sample": sample},
@@ -207,7 +216,7 @@ def main():
     rc = d_rc.cpu().numpy()
     stats = d_st.cpu().numpy()
     ok = int((rc == 1).sum())
-    ftraj, f_step, dense_step, steps = flops_per_trajectory(flops, n, ns, stats)
+    ftraj, f_step, dense_step, steps = flops_per_trajectory(flops, n, ns, stats, spec.alg)
     peak = _lib.measure_fp64_peak(0)
     achieved = float(ftraj.sum()) * args.steps / (dev_ms * 1e-3)
     traffic = None
@@ -247,7 +256,7 @@ def main():
     d2h = 8 * N * n * ns + N * (8 + 4 + 20) + 8 * (2 * ns * n + 1)
 
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": metric_name(spec), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(spec, N), "full_size": N == spec.n_total,

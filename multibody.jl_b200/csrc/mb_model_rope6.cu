@@ -1,0 +1,7 @@
+// Kernel set of model 'rope6' (C5, documented size: stiff 6-link rope, n = 42).
+#include "mb_model_def.cuh"
+#define MB_FN static __device__ __forceinline__
+#define MB_RESTRICT __restrict__
+#define MB_NO_PATTERN
+#include "generated/mbm_rope6.h"
+MB_DEFINE_MODEL(rope6, 128, 1, 0)

@@ -61,8 +61,11 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C4":    # Robot6DOF parameter sweep, 1M, Rodas5P reltol 1e-8 (test/test_robot.jl:268-288)
         total, model, alg, tol = 1 << 20, "robot6dof", "rodas5p", 1e-8
         saveat = np.linspace(0.0, 2.0, 21)
+    elif config == "C5":    # stiff 6-link rope of docs/src/examples/ropes_and_cables.md:24-36, 64k parameter sets
+        total, model, alg, tol = 1 << 16, "rope6", "rodas5p", 1e-6
+        saveat = np.linspace(0.0, 5.0, 51)[1:]
     else:
-        raise KeyError(f"config {config} is not built yet (C1, C2, C3, C4 are)")
+        raise KeyError(f"config {config} is not built (C1..C5 are; C5 at the documented 6-link size)")
     N = total if N is None else int(N)
     sys = get_model(model)
     idx = np.arange(offset, offset + N, dtype=np.int64)
@@ -81,6 +84,10 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
         P[sys.param_index("body2.m")] = m
     elif config == "C3":
         U[sys.state_index("j1.w")] = uniform(idx, 0, 3.0, 7.0)
+    elif config == "C5":
+        P[sys.param_index("rope.d_joint")] = uniform(idx, 0, 0.5, 2.0)
+        P[sys.param_index("body.m")] = uniform(idx, 1, 0.5, 2.0)
+        P[sys.param_index("rope.air_resistance")] = uniform(idx, 2, 0.0, 0.4)
     elif config == "C4":
         P[sys.param_index("mechanics.load.m")] = uniform(idx, 0, 5.0, 25.0)
         for a in range(6):

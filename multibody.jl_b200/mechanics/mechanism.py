@@ -197,8 +197,11 @@ class Mechanism:
 
         def apply():
             acc = vsub(fr.a0, self.gvec)
-            if not _is_zero(air_resistance):
-                nv = sqrt(dot(fr.v0, fr.v0))
+            v2 = dot(fr.v0, fr.v0)
+            if not _is_zero(air_resistance) and isinstance(v2, Ex):
+                # |v| v; the 1e-300 keeps d|v|/dv = v/|v| finite (= 0) at rest, where the
+                # reference's finite-difference Jacobian (autodiff=false) sees 0 as well
+                nv = sqrt(v2 + 1e-300)
                 acc = vadd(acc, vscale(air_resistance * nv, fr.v0))
             lin = vadd(matvec(fr.R, acc),
                        vadd(cross(fr.z, r_cm), cross(fr.w, cross(fr.w, r_cm))))

@@ -148,11 +148,40 @@ def static_pivots(sysm: ReducedSystem, h: float = 1e-3):
     return choose_pivots_numeric(W)
 
 
+def rope(n_links: int = 6, name: str = "rope6") -> ReducedSystem:
+    """C5 (first milestone: the documented size).  Stiff `Rope(l=1, m=6, n=6, d_joint=1,
+    dir=[0.05,1,0])` hung from the world with a `Body` at its end
+    (docs/src/examples/ropes_and_cables.md:24-36; Rope: src/components.jl:574-626):
+    n+1 `Spherical(state=true, d=d_joint)` joints (Euler angles, sequence [1,2,3],
+    src/joints.jl:181-259) and n `BodyShape(m = m/n, r = l/n dir)` links.
+    States: 6 (n+1) = 42 for n = 6."""
+    mb = ModelBuilder(name)
+    mech = Mechanism(mb)
+    d_joint = mb.param("rope.d_joint", 1.0)
+    m_body = mb.param("body.m", 1.0)
+    air = mb.param("rope.air_resistance", 0.0)
+    l, m_rope = 1.0, 6.0
+    dirv = np.array([0.05, 1.0, 0.0])
+    dirv = dirv / np.linalg.norm(dirv)
+    li, mi = l / n_links, m_rope / n_links
+    fr = mech.world()
+    for i in range(n_links + 1):
+        phi = [mb.state(f"rope.joint_{i+1}.phi[{k+1}]", 0.0) for k in range(3)]
+        phid = [mb.state(f"rope.joint_{i+1}.phid[{k+1}]", 0.0) for k in range(3)]
+        fr = mech.spherical(fr, phi, phid, d=d_joint)
+        if i < n_links:
+            fr = mech.body_shape(fr, tuple(li * dirv), mi, air_resistance=air)
+    mech.body(fr, m_body, (0.0, 0.0, 0.0))
+    mech.solve_accelerations()
+    return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+
+
 MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "pendulum": pendulum,
     "spring_damper": spring_damper,
     "robot6dof": robot6dof,
     "fourbar": fourbar,
+    "rope6": rope,
 }
 _cache: Dict[str, ReducedSystem] = {}
 

@@ -7,6 +7,7 @@
 #ifndef MBO_INTERP_H
 #define MBO_INTERP_H
 #include <math.h>
+#include <stddef.h>
 static inline double mbo_interp(const double* tb, int table, double t, int cubic, int deriv) {
   const double t0 = tb[0], h = tb[1];
   const int nk = (int)tb[2];

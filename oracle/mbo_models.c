@@ -1,36 +1,14 @@
 /* ORACLE -- test infrastructure only. Never linked into the product.
- * Model table: the generated right-hand sides (csrc/generated/mbm_*.h, emitted from the
- * restated reference equations) compiled as plain C. */
+ * Model table; one translation unit per model (mbo_model_<name>.c). */
 #include <string.h>
 #include "mbo.h"
-#include "mbo_interp.h"
-#define MB_FN static
-#define MB_RESTRICT restrict
-#include "../multibody.jl_b200/csrc/generated/mbm_pendulum.h"
-#include "../multibody.jl_b200/csrc/generated/mbm_spring_damper.h"
-#include "../multibody.jl_b200/csrc/generated/mbm_robot6dof.h"
-#ifdef MBO_HAVE_FOURBAR
-#include "../multibody.jl_b200/csrc/generated/mbm_fourbar.h"
-#endif
-#ifdef MBO_HAVE_ROPE
-#include "../multibody.jl_b200/csrc/generated/mbm_rope6.h"
-#endif
-
-#define ENTRY(X) {#X, MBM_##X##_N, MBM_##X##_M, MBM_##X##_NNZ, mbm_##X##_jrow, mbm_##X##_jcol, mbm_##X##_mass, \
-                  mbm_##X##_rhs, mbm_##X##_jac, mbm_##X##_dT, MBM_##X##_NLU, mbm_##X##_factor, mbm_##X##_solve}
-static const mbo_model MODELS[] = {
-  ENTRY(pendulum), ENTRY(spring_damper), ENTRY(robot6dof),
-#ifdef MBO_HAVE_FOURBAR
-  ENTRY(fourbar),
-#endif
-#ifdef MBO_HAVE_ROPE
-  ENTRY(rope6),
-#endif
-};
+extern const mbo_model mbo_model_pendulum, mbo_model_spring_damper, mbo_model_robot6dof, mbo_model_fourbar, mbo_model_rope6;
+static const mbo_model* const MODELS[] = {&mbo_model_pendulum, &mbo_model_spring_damper, &mbo_model_robot6dof,
+                                          &mbo_model_fourbar, &mbo_model_rope6};
 
 const mbo_model* mbo_find_model(const char* name) {
   for (unsigned i = 0; i < sizeof(MODELS) / sizeof(MODELS[0]); i++)
-    if (strcmp(MODELS[i].name, name) == 0) return &MODELS[i];
+    if (strcmp(MODELS[i]->name, name) == 0) return MODELS[i];
   return 0;
 }
 int mbo_model_dims(const char* name, int* n, int* m, int* nnz) {

@@ -98,3 +98,43 @@ def robot_rhs(u, p, q_ref, qd_ref):
     du[0:12:2] = w
     du[1:12:2] = qdd
     return du
+
+
+# ---- rope (C5): independent forward kinematics for the energy check -------------------------
+def _axis_rot_T(k, a):
+    """local->world elementary rotation about axis k (1-based)."""
+    return rodrigues([1.0 if i == k - 1 else 0.0 for i in range(3)], a)
+
+
+def rope_energy(u, m_body, n_links=6, l=1.0, m_rope=6.0, dirv=(0.05, 1.0, 0.0)):
+    """Total mechanical energy of the stiff rope of docs/src/examples/ropes_and_cables.md:24-36
+    from the Euler-angle states (sequence [1,2,3]); velocities by differencing the forward
+    kinematics along the state velocity, so nothing is shared with the product's equations."""
+    dirv = np.asarray(dirv, float) / np.linalg.norm(dirv)
+    li, mi = l / n_links, m_rope / n_links
+
+    def fk(phis):
+        T = np.eye(3)
+        p = np.zeros(3)
+        out = []
+        for i in range(n_links + 1):
+            a = phis[3 * i:3 * i + 3]
+            # R = A3 A2 A1 is world->local (orientation.jl:288-299), so local->world appends A1' A2' A3'
+            T = T @ _axis_rot_T(1, a[0]) @ _axis_rot_T(2, a[1]) @ _axis_rot_T(3, a[2])
+            if i < n_links:
+                out.append((mi, p + T @ (li / 2 * dirv), T.copy()))
+                p = p + T @ (li * dirv)
+            else:
+                out.append((m_body, p.copy(), T.copy()))
+        return out
+    phi = np.concatenate([u[6 * i:6 * i + 3] for i in range(n_links + 1)])
+    phid = np.concatenate([u[6 * i + 3:6 * i + 6] for i in range(n_links + 1)])
+    eps = 1e-6
+    b0, bp, bm = fk(phi), fk(phi + eps * phid), fk(phi - eps * phid)
+    E = 0.0
+    for (m, c, T), (_, cp, Tp), (_, cm, Tm) in zip(b0, bp, bm):
+        v = (cp - cm) / (2 * eps)
+        Wm = ((Tp - Tm) / (2 * eps)) @ T.T
+        w = np.array([Wm[2, 1], Wm[0, 2], Wm[1, 0]])
+        E += 0.5 * m * v @ v + 0.5 * 0.001 * w @ w + m * 9.80665 * c[1]
+    return E

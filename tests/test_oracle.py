@@ -91,6 +91,28 @@ def test_fourbar_initial_configuration_is_consistent():
     assert sysm.u0[sysm.state_index("j2.s")] == pytest.approx(-0.2)   # the reference's s guess is already consistent
 
 
+def test_rope_energy_balance_with_independent_kinematics(oracle):
+    """C5 (docs/src/examples/ropes_and_cables.md:24-36; Rope src/components.jl:574-626): without
+    joint damping the energy computed by an independent numpy forward kinematics is conserved;
+    with d_joint > 0 (Spherical d, src/joints.jl:213-222) it only decreases; retcode success is
+    all the reference asserts (test/basic_tests.jl:920)."""
+    from ref_models import rope_energy
+    sysm = get_model("rope6")
+    assert sysm.n == 42                                     # 6 (N + 1), SURVEY.md 8a row a14
+    tb = sysm.tables.pack()
+    sv = np.linspace(0.0, 2.0, 21)
+    p = sysm.p0.copy()
+    p[sysm.param_index("rope.d_joint")] = 0.0
+    r = oracle.solve("rope6", "rodas5p", sysm.u0[:, None], p[:, None], tb, (0.0, 2.0), sv, abstol=1e-8, reltol=1e-8)
+    assert r["retcode"][0] == 1
+    E = np.array([rope_energy(r["u"][k, :, 0], p[1]) for k in range(len(sv))])
+    assert np.abs(E - E[0]).max() < 1e-5 * abs(E[0])
+    r = oracle.solve("rope6", "rodas5p", sysm.u0[:, None], sysm.p0[:, None], tb, (0.0, 2.0), sv, abstol=1e-8, reltol=1e-8)
+    assert r["retcode"][0] == 1
+    E = np.array([rope_energy(r["u"][k, :, 0], sysm.p0[1]) for k in range(len(sv))])
+    assert (np.diff(E) < 1e-6).all() and E[-1] < E[0] - 10.0
+
+
 def test_robot_forward_difference_jacobian_mode_agrees(oracle):
     """`Rodas5P(autodiff=false)` (test/test_robot.jl:288) uses finite-difference J; a W-method
     tolerates the difference: same trajectory within the north-star tolerance."""
