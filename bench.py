@@ -134,7 +134,8 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(spec, full), "sample": sample},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{sample} trajectories of the same workload per step (same RNG stream), all {cores} host threads"},
+                         "sample": f"first {sample} trajectories of the same workload per step (same RNG stream), all {cores} host threads, "
+                                   f"{dt / args.steps:.1f} s per step"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
@@ -275,17 +276,19 @@ def main():
                      "hbm_gbs_algorithmic": (h2d + d2h) * args.steps / (dev_ms * 1e-3) / 1e9},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sys.path.insert(0, os.path.join(ROOT, "oracle"))
-        import mbo
+        # the oracle on the host cores, in a fresh interpreter (no torch/OpenMP worker threads
+        # spinning next to the oracle's pthreads); bounded sample of the same workload
         cores = os.cpu_count() or 1
         sample = args.cpu_sample or max(256, 256 * cores)
-        cs = ensembles.make_ensemble(args.config, sample)
-        t0 = time.perf_counter()
-        r = mbo.solve(cs.model, cs.alg, cs.u0, cs.p, sys_.tables.pack(), cs.tspan, cs.saveat, abstol=cs.abstol,
-                      reltol=cs.reltol, nthreads=cores)
-        dtc = time.perf_counter() - t0
-        out["cpu_baseline"] = {"value": sample / dtc, "unit": UNIT, "cores": cores, "kind": "port",
-                               "sample": f"first {sample} trajectories of the same workload, {cores} host threads, {dtc:.1f} s"}
+        r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--config", args.config,
+                            "--steps", "1", "--warmup", "0", "--cpu-sample", str(sample)],
+                           capture_output=True, text=True, env={k: v for k, v in os.environ.items()
+                                                                if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
+        try:
+            out["cpu_baseline"] = json.loads(r.stdout.strip().splitlines()[-1])["cpu_baseline"]
+        except Exception as e:   # keep the GPU line even if the CPU leg failed
+            out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"failed: {e}: {r.stderr[-200:]}"}
     if rank == 0:
         print(json.dumps(out))
     if world > 1:

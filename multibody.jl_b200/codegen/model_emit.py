@@ -217,6 +217,8 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(f"// algorithmic flops (BASELINE.md sec.4 table): rhs={code.F_rhs} jac={code.F_jac} "
                f"dT={code.F_dT} factor(jac+LU)={code.F_factor} solve={code.F_solve}")
     out.append("#pragma once")
+    for nm in ("RHS", "FACTOR", "SOLVE"):      # per-function linkage override (tuning)
+        out.append(f"#ifndef MB_FN_{nm}\n#define MB_FN_{nm} MB_FN\n#endif")
     out.append(f"#define MBM_{X}_N {n}")
     out.append(f"#define MBM_{X}_M {max(m, 0)}")
     out.append(f"#define MBM_{X}_NNZ {code.nnz}")
@@ -245,7 +247,7 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append("  return (int)((w[i >> 6] >> (i & 63)) & 1ull);")
     out.append("}")
     out.append("")
-    out.append(pr.function(f"MB_FN void mbm_{X}_rhs({args}, double* MB_RESTRICT du)",
+    out.append(pr.function(f"MB_FN_RHS void mbm_{X}_rhs({args}, double* MB_RESTRICT du)",
                            [(f"du[{i}]", sys.rhs[i]) for i in range(n)]))
     out.append("")
     out.append(pr.function(f"MB_FN void mbm_{X}_jac({args}, double* MB_RESTRICT Jnz)",
@@ -255,11 +257,11 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
                            [(f"dT[{i}]", code.dT_nodes[i]) for i in range(n)]))
     out.append("")
     lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)]
-    out.append(pr.function(f"MB_FN void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
+    out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     out.append("")
     spr = Printer(code.solve_graph, {"lu": "LU[{i}]", "b": "b{i}", "c": "c", "p": "p[{i}]"})
-    sol_lines = [f"MB_FN void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "
+    sol_lines = [f"MB_FN_SOLVE void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "
                  f"double* MB_RESTRICT b) {{"]
     for i in range(n):
         sol_lines.append(f"  const double b{i} = b[{i}];")

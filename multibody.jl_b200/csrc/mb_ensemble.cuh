@@ -158,7 +158,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
     }
     // block-wide barrier + vote: keeps the warps of a CTA in step, so the (large) straight-line
     // instruction stream is fetched once per CTA per step instead of once per warp
+#ifdef MB_NO_LOCKSTEP
+    if (!__any_sync(FULL, active)) break;
+#else
     if (!__syncthreads_or(active)) break;
+#endif
     if (active && rc == RC_DEFAULT) {
       ++iter;
       if (iter > maxiters) rc = RC_MAXITERS;

@@ -3,6 +3,7 @@
 // Tsit5 and Rodas5P kernels and registers a launcher.
 #pragma once
 #include "mb_ensemble.cuh"
+#include "mb_rodas_rows.cuh"
 #include "mb_registry.h"
 #include <cstdlib>
 
@@ -12,6 +13,13 @@ static inline int mb_cap_ctas_per_sm(int bps) {
   const int cap = e ? atoi(e) : 0;
   return (cap > 0 && cap < bps) ? cap : bps;
 }
+
+// MB_RODAS_CLASSIC selects the first Rodas5P kernel (vectors as separate local arrays)
+#ifdef MB_RODAS_CLASSIC
+#define MB_RODAS_KERNEL(MODEL, BLOCK, MINB, UNR) mbk::ensemble_kernel<MODEL, 2, BLOCK, MINB, UNR>
+#else
+#define MB_RODAS_KERNEL(MODEL, BLOCK, MINB, UNR) mbk::rodas5p_rows_kernel<MODEL, BLOCK, MINB>
+#endif
 
 #define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
   struct MbModel_##X {                                                                              \
@@ -47,7 +55,7 @@ static inline int mb_cap_ctas_per_sm(int bps) {
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, 0, st>>>(a);                                                    \
     } else if (alg == 2) {                                                                          \
-      auto kern = mbk::ensemble_kernel<MbModel_##X, 2, BLOCK, MINB, UNR>;                           \
+      auto kern = MB_RODAS_KERNEL(MbModel_##X, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 0);                \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, 0);                          \
       bps = mb_cap_ctas_per_sm(bps);                                                                \

@@ -3,6 +3,18 @@
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__
 #define MB_NO_PATTERN
+#ifdef MB_R_RHS_NOINLINE
+#define MB_FN_RHS static __device__ __noinline__
+#endif
+#ifdef MB_R_FACTOR_NOINLINE
+#define MB_FN_FACTOR static __device__ __noinline__
+#endif
+#ifdef MB_R_SOLVE_NOINLINE
+#define MB_FN_SOLVE static __device__ __noinline__
+#endif
+#ifndef MB_R_UNR
+#define MB_R_UNR 0
+#endif
 #include "generated/mbm_robot6dof.h"
 #ifndef MB_R_BLOCK
 #define MB_R_BLOCK 256
@@ -11,4 +23,4 @@
 #define MB_R_MINB 1
 #endif
 #define MB_EXPAND(...) MB_DEFINE_MODEL(__VA_ARGS__)
-MB_EXPAND(robot6dof, MB_R_BLOCK, MB_R_MINB, 0)
+MB_EXPAND(robot6dof, MB_R_BLOCK, MB_R_MINB, MB_R_UNR)

@@ -1,0 +1,193 @@
+// Rodas5P ensemble kernel, "row workspace" variant.
+//
+// Same algorithm and arithmetic as the Rodas5P branch of mbk::ensemble_kernel
+// (mb_ensemble.cuh); what differs is where the per-trajectory vectors live.  Every vector
+// (8 stage vectors k, stage state, C-sum, u, df/dt, parameters, LU slots) is a row of ONE
+// thread-local array that is also indexed dynamically (the rolled stage loop), so the
+// compiler keeps all of it in local memory and loads each value where it is used.  In the
+// first version the stage state, the C-sum and the right-hand side output (3 x 36 doubles =
+// 216 of the 255 registers) were live in registers across the inlined rhs(), which left its
+// 2 400-flop body ~40 registers: 300 LDL + 155 STL of spill code, executed 8 times per step.
+#pragma once
+#include "mb_ensemble.cuh"
+
+namespace mbk {
+
+template <class M, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs a) {
+  constexpr int N = M::N;
+  constexpr int NPR = (M::NP + N - 1) / N > 0 ? (M::NP + N - 1) / N : 1;
+  constexpr int NLUR = (M::NLU + N - 1) / N > 0 ? (M::NLU + N - 1) / N : 1;
+  constexpr int R_US = 8, R_SC = 9, R_U = 10, R_DT = 11, R_P = 12, R_LU = R_P + NPR, ROWS = R_LU + NLUR;
+  constexpr unsigned FULL = 0xffffffffu;
+  constexpr double EPS = 2.220446049250313e-16;
+
+  double W[ROWS][N];
+  double* const us = &W[R_US][0];
+  double* const sc = &W[R_SC][0];
+  double* const u = &W[R_U][0];
+  double* const dT = &W[R_DT][0];
+  double* const p = &W[R_P][0];
+  double* const LU = &W[R_LU][0];
+  double t = 0.0, dt = 0.0, qold = QOLDINIT;
+  long long traj = -1, iter = 0;
+  int is = 0, naccept = 0, nreject = 0, nf = 0, njac = 0, nsolve = 0;
+  bool active = false, drained = false;
+  const double dtmax = a.dtmax > 0.0 ? a.dtmax : (a.t1 - a.t0);
+  const long long maxiters = a.maxiters > 0 ? a.maxiters : 100000;
+  const double* __restrict__ tb = a.tb;
+
+  for (;;) {
+    int rc = RC_DEFAULT;
+    if (!active && !drained) {
+      const unsigned long long idx = atomicAdd(a.queue, 1ull);
+      if (idx >= (unsigned long long)a.N) {
+        drained = true;
+      } else {
+        traj = (long long)idx;
+#pragma unroll
+        for (int i = 0; i < N; i++) u[i] = a.u0[(size_t)i * a.N + traj];
+#pragma unroll
+        for (int i = 0; i < M::NP; i++) p[i] = a.p[(size_t)i * a.N + traj];
+        t = a.t0; is = 0; iter = 0; qold = QOLDINIT;
+        naccept = nreject = nf = njac = nsolve = 0;
+        while (is < a.n_save && a.saveat[is] <= t) {
+          if (a.saveat[is] == t) {
+#pragma unroll
+            for (int i = 0; i < N; i++) a.out_u[((size_t)is * N + i) * a.N + traj] = u[i];
+          }
+          is++;
+        }
+        if (a.dt0 > 0.0) dt = a.dt0;
+        else {
+          dt = initial_dt<M>(*reinterpret_cast<const double(*)[N]>(u), p, tb, a.t0, dtmax, a.abstol, a.reltol);
+          nf += 2;
+        }
+        active = true;
+        if (!(t < a.t1)) rc = RC_SUCCESS;
+      }
+    }
+    if (!__syncthreads_or(active)) break;     // block-lockstep stepping (see mb_ensemble.cuh)
+    if (active && rc == RC_DEFAULT) {
+      ++iter;
+      if (iter > maxiters) rc = RC_MAXITERS;
+      else if (!isfinite(dt)) rc = RC_DTNAN;
+      else if (dt < fmax(a.dtmin, 16.0 * EPS * fmax(fabs(t), 1e-300))) rc = RC_DTLESSTHANMIN;
+    }
+    if (active && rc == RC_DEFAULT) {
+      bool last = false;
+      if (t + dt >= a.t1 - 100.0 * EPS * fabs(a.t1)) { dt = a.t1 - t; last = true; }
+      const double cW = 1.0 / (dt * RD_GAMMA);
+      M::factor(u, p, t, tb, cW, LU);
+      njac++;
+      if (M::HAS_DT) M::dT(u, p, t, tb, dT);
+      const double inv_dt = 1.0 / dt;
+#pragma unroll 1
+      for (int s = 0; s < 8; s++) {
+        {
+          double x[N], y[N];
+#pragma unroll
+          for (int i = 0; i < N; i++) { x[i] = u[i]; y[i] = 0.0; }
+#pragma unroll 1
+          for (int j = 0; j < s; j++) {
+            const double aj = cRD_A[s][j], cj = cRD_C[s][j];
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+              const double kj = W[j][i];
+              x[i] = fma(aj, kj, x[i]);
+              y[i] = fma(cj, kj, y[i]);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < N; i++) { us[i] = x[i]; sc[i] = y[i]; }
+        }
+        M::rhs(us, p, t + cRD_CT[s] * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
+        {
+          double r[N];
+          const double dd = dt * cRD_D[s];
+#pragma unroll
+          for (int i = 0; i < N; i++) {
+            double v = W[s][i];
+            if (M::HAS_DT) v = fma(dd, dT[i], v);
+            if (M::isdiff(i)) v = fma(sc[i], inv_dt, v);
+            r[i] = v;
+          }
+          M::solve(LU, cW, p, r);
+#pragma unroll
+          for (int i = 0; i < N; i++) W[s][i] = r[i];
+        }
+      }
+      nf += 8; nsolve += 8;
+      // u_new = us + k8; error estimate = k8
+      double EEst;
+      {
+        double sacc = 0.0;
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+          const double k8 = W[7][i], ua = u[i], ub = us[i] + k8;
+          const double scl = a.abstol + fmax(fabs(ua), fabs(ub)) * a.reltol;
+          const double q = k8 / scl;
+          sacc += q * q;
+        }
+        EEst = sqrt(sacc / N);
+      }
+      if (!isfinite(EEst)) {
+        rc = RC_DTNAN;
+      } else {
+        double q, q11 = 0.0;
+        if (EEst == 0.0) q = 1.0 / QMAX;
+        else {
+          q11 = pow(EEst, BETA1);
+          q = q11 / pow(qold, BETA2);
+          q = fmax(1.0 / QMAX, fmin(1.0 / QMIN, q / SAFETY));
+        }
+        if (EEst <= 1.0) {
+          naccept++;
+          const double tn = last ? a.t1 : t + dt;
+          while (is < a.n_save && a.saveat[is] <= tn) {       // saveat via dense output
+            const double ts = a.saveat[is];
+            double* __restrict__ o = a.out_u + (size_t)is * N * a.N + traj;
+            if (ts == tn) {
+#pragma unroll
+              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = us[i] + W[7][i];
+            } else {
+              const double th = (ts - t) / dt;
+              for (int i = 0; i < N; i++) {
+                double K1 = 0, K2 = 0, K3 = 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                  const double kj = W[j][i];
+                  K1 = fma(RD_H[0][j], kj, K1); K2 = fma(RD_H[1][j], kj, K2); K3 = fma(RD_H[2][j], kj, K3);
+                }
+                const double un = us[i] + W[7][i];
+                o[(size_t)i * a.N] = (1.0 - th) * u[i] + th * (un + (1.0 - th) * (K1 + th * (K2 + th * K3)));
+              }
+            }
+            is++;
+          }
+#pragma unroll
+          for (int i = 0; i < N; i++) u[i] = us[i] + W[7][i];
+          t = tn;
+          qold = fmax(EEst, QOLDINIT);
+          dt = fmin(dt / q, dtmax);
+          if (!(t < a.t1)) rc = RC_SUCCESS;
+        } else {
+          nreject++;
+          dt = dt / fmin(1.0 / QMIN, q11 / SAFETY);
+        }
+      }
+    }
+    if (active && rc != RC_DEFAULT) {
+      a.out_tfinal[traj] = t;
+      a.retcode[traj] = rc;
+      a.stats[0 * a.N + traj] = naccept; a.stats[1 * a.N + traj] = nreject; a.stats[2 * a.N + traj] = nf;
+      a.stats[3 * a.N + traj] = njac; a.stats[4 * a.N + traj] = nsolve;
+      const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+      for (; is < a.n_save; is++)
+        for (int i = 0; i < N; i++) a.out_u[((size_t)is * N + i) * a.N + traj] = qnan;
+      active = false;
+    }
+  }
+}
+
+}  // namespace mbk
