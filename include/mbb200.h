@@ -108,6 +108,14 @@ int mbb200_solve_device(mbb200_model* model, const mbb200_opts* opts, int dev_in
                         double* d_out_u, double* d_out_tfinal, int32_t* d_retcode, int32_t* d_stats,
                         double* d_reduce_out);
 
+/* Observed (eliminated) variables of saved states -- the `sol(tv, idxs = expr)` read-back every
+ * reference assertion goes through (test/test_robot.jl:321-325).  `u` is the
+ * out_u of a solve ([n_save][n][N], host), out_obs is [n_save][nobs][N]; the order of the
+ * nobs variables is fixed by the model (generated header comment / ReducedSystem.observed_names). */
+int mbb200_model_observed_count(const mbb200_model* model, int32_t* nobs);
+int mbb200_observed(mbb200_model* model, int64_t N, const double* u, const double* p, const double* saveat,
+                    int32_t n_save, double* out_obs);
+
 /* Device time (ms, CUDA events on the launching stream) and number of kernel launches of
  * the most recent solve call on device `dev_index`. */
 int mbb200_last_timing(int dev_index, double* kernel_ms, int32_t* n_launches);

@@ -24,7 +24,7 @@ RC_NAMES = {0: "Default", 1: "Success", 3: "DtNaN", 4: "MaxIters", 5: "DtLessTha
 SYMBOLS = [
     "mbb200_abi_version", "mbb200_init", "mbb200_init_devices", "mbb200_device_count",
     "mbb200_model_load", "mbb200_model_info", "mbb200_model_flops", "mbb200_model_free",
-    "mbb200_solve", "mbb200_solve_device", "mbb200_last_timing", "mbb200_measure_fp64_peak",
+    "mbb200_solve", "mbb200_solve_device", "mbb200_model_observed_count", "mbb200_observed", "mbb200_last_timing", "mbb200_measure_fp64_peak",
     "mbb200_dev_alloc", "mbb200_dev_free", "mbb200_dev_upload", "mbb200_dev_download",
     "mbb200_host_alloc_pinned", "mbb200_host_free_pinned", "mbb200_last_error", "mbb200_shutdown",
 ]
@@ -74,6 +74,8 @@ def lib() -> C.CDLL:
         L.mbb200_solve.argtypes = [vp, C.POINTER(Opts), C.c_int64, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.mbb200_solve_device.argtypes = [vp, C.POINTER(Opts), C.c_int, C.c_int64, vp, vp, vp, C.c_int32,
                                           vp, vp, vp, vp, vp]
+        L.mbb200_model_observed_count.argtypes = [vp, ip]
+        L.mbb200_observed.argtypes = [vp, C.c_int64, vp, vp, vp, C.c_int32, vp]
         L.mbb200_last_timing.argtypes = [C.c_int, dp, ip]
         L.mbb200_measure_fp64_peak.argtypes = [C.c_int, dp]
         L.mbb200_dev_alloc.argtypes = [C.c_int, C.c_size_t, C.POINTER(vp)]

@@ -152,6 +152,8 @@ class EnsembleSolution:
     reduction: Optional[Dict[str, np.ndarray]] = None
     kernel_ms: float = 0.0
     gpu_launches: int = 0
+    p: Optional[np.ndarray] = None      # [m][N] parameters of the trajectories (for observed())
+    _obs: Optional[np.ndarray] = None
 
     def __len__(self):
         return self.u.shape[2]
@@ -160,6 +162,29 @@ class EnsembleSolution:
         names = ("naccept", "nreject", "nf", "njac", "nsolve")
         return TrajectorySolution(self.t, self.u[:, :, i], int(self.retcode[i]),
                                   {k: int(self.stats[j, i]) for j, k in enumerate(names)}, self.sys)
+
+    def observed(self, names=None) -> Dict[str, np.ndarray]:
+        """`sol(t, idxs = expr)` for eliminated variables (test/test_robot.jl:321-325): evaluates
+        the model's observed expressions on the device for every saved state.  Returns
+        {name: [n_save][N]} (all observed variables, or the requested ones)."""
+        sys = self.sys
+        all_names = sys.observed_names
+        if not all_names:
+            raise KeyError(f"{sys.name} defines no observed variables")
+        want = list(all_names) if names is None else ([names] if isinstance(names, str) else list(names))
+        for nm in want:
+            if nm not in all_names:
+                raise KeyError(f"{nm!r} is not an observed variable of {sys.name}; available: {all_names}")
+        if self._obs is None:
+            ns, n, N = self.u.shape
+            out = np.empty((ns, len(all_names), N))
+            h = _handles[sys.name]
+            P = np.ascontiguousarray(self.p) if sys.m else None
+            _lib.check(_lib.lib().mbb200_observed(h.handle, N, _lib.ptr(np.ascontiguousarray(self.u)),
+                                                  _lib.ptr(P) if sys.m else None, _lib.ptr(np.ascontiguousarray(self.t)),
+                                                  ns, _lib.ptr(out)))
+            self._obs = out
+        return {nm: self._obs[:, all_names.index(nm), :] for nm in want}
 
     def state(self, name: str) -> np.ndarray:
         """[n_save][N] values of one named state."""
@@ -231,4 +256,4 @@ def solve(eprob: Union[EnsembleProblem, ODEProblem], alg, ensemblealg: Optional[
     if reduction:
         from .distributed import allreduce_statistics, finalize_statistics
         redd = finalize_statistics(allreduce_statistics(red), ns, n)   # no-op outside torch.distributed
-    return EnsembleSolution(sys, sv, out, tf, rc, st, redd, ms, nl)
+    return EnsembleSolution(sys, sv, out, tf, rc, st, redd, ms, nl, P[:sys.m] if sys.m else None)

@@ -228,6 +228,8 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(f"#define MBM_{X}_F_DT {code.F_dT}")
     out.append(f"#define MBM_{X}_F_FACTOR {code.F_factor}")
     out.append(f"#define MBM_{X}_F_SOLVE {code.F_solve}")
+    obs_names = sorted(sys.observed)
+    out.append(f"#define MBM_{X}_NOBS {len(obs_names)}")
     out.append(f"#define MBM_{X}_HAS_DT {1 if any(d != g.zero for d in code.dT_nodes) else 0}")
     out.append(f"#define MBM_{X}_IS_ODE {1 if all(sys.mass_diag) else 0}")
     out.append("#ifndef MB_NO_PATTERN")
@@ -255,6 +257,10 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append("")
     out.append(pr.function(f"MB_FN void mbm_{X}_dT({args}, double* MB_RESTRICT dT)",
                            [(f"dT[{i}]", code.dT_nodes[i]) for i in range(n)]))
+    out.append("")
+    out.append(f"// observed variables, in this order: {', '.join(obs_names) if obs_names else '(none)'}")
+    out.append(pr.function(f"MB_FN void mbm_{X}_observed({args}, double* MB_RESTRICT obs)",
+                           [(f"obs[{k}]", sys.observed[nm]) for k, nm in enumerate(obs_names)]))
     out.append("")
     lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)]
     out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",

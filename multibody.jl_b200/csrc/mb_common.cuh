@@ -103,3 +103,14 @@ struct MbArgs {
   double t0, t1, abstol, reltol, dt0, dtmin, dtmax;
   long long maxiters;
 };
+
+// ---- observed-variable evaluation (the step after the solve: `sol(t, idxs = expr)`) ----------
+struct MbObsArgs {
+  long long N;            // trajectories
+  int n_save;
+  const double* u;        // [n_save][n][N] saved states
+  const double* p;        // [m][N]
+  const double* tb;       // packed tables
+  const double* saveat;   // [n_save]
+  double* out;            // [n_save][nobs][N]
+};

@@ -14,6 +14,26 @@ static inline int mb_cap_ctas_per_sm(int bps) {
   return (cap > 0 && cap < bps) ? cap : bps;
 }
 
+// Observed variables of saved states: one thread per (save point, trajectory); HBM-bound
+// (reads n + m doubles, writes nobs doubles per point; coalesced along the trajectory index).
+template <class M, int NOBS>
+__global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
+  constexpr int N = M::N, NP = (M::NP > 0 ? M::NP : 1), NO = (NOBS > 0 ? NOBS : 1);
+  const long long total = a.N * (long long)a.n_save;
+  for (long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x; g < total; g += (long long)gridDim.x * blockDim.x) {
+    const int is = (int)(g / a.N);
+    const long long j = g - (long long)is * a.N;
+    double u[N], p[NP], o[NO];
+#pragma unroll
+    for (int i = 0; i < N; i++) u[i] = a.u[((size_t)is * N + i) * a.N + j];
+#pragma unroll
+    for (int i = 0; i < M::NP; i++) p[i] = a.p[(size_t)i * a.N + j];
+    M::observed(u, p, a.saveat[is], a.tb, o);
+#pragma unroll
+    for (int k = 0; k < NOBS; k++) a.out[((size_t)is * NOBS + k) * a.N + j] = o[k];
+  }
+}
+
 // MB_RODAS_CLASSIC selects the first Rodas5P kernel (vectors as separate local arrays)
 #ifdef MB_RODAS_CLASSIC
 #define MB_RODAS_KERNEL(MODEL, BLOCK, MINB, UNR) mbk::ensemble_kernel<MODEL, 2, BLOCK, MINB, UNR>
@@ -42,6 +62,10 @@ static inline int mb_cap_ctas_per_sm(int bps) {
       mbm_##X##_solve(LU, c, p, b);                                                                 \
     }                                                                                               \
     static __device__ __forceinline__ int isdiff(int i) { return mbm_##X##_isdiff(i); }             \
+    static __device__ __forceinline__ void observed(const double* u, const double* p, double t,    \
+                                                    const double* tb, double* o) {                  \
+      mbm_##X##_observed(u, p, t, tb, o);                                                           \
+    }                                                                                               \
   };                                                                                                \
   static cudaError_t mb_launch_##X(int alg, const MbArgs& a, int sm_count, cudaStream_t st) {       \
     int bps = 1;                                                                                    \
@@ -68,11 +92,18 @@ static inline int mb_cap_ctas_per_sm(int bps) {
     }                                                                                               \
     return cudaGetLastError();                                                                      \
   }                                                                                                 \
+  static cudaError_t mb_launch_obs_##X(const MbObsArgs& a, int sm_count, cudaStream_t st) {         \
+    long long blocks = (a.N * (long long)a.n_save + 255) / 256;                                     \
+    if (blocks > (long long)sm_count * 8) blocks = (long long)sm_count * 8;                         \
+    if (blocks < 1) blocks = 1;                                                                     \
+    mb_observed_kernel<MbModel_##X, MBM_##X##_NOBS><<<(unsigned)blocks, 256, 0, st>>>(a);           \
+    return cudaGetLastError();                                                                      \
+  }                                                                                                 \
   static MbKernelEntry mb_entry_##X = {#X, MBM_##X##_N, MBM_##X##_M, MBM_##X##_NLU,                 \
                                        MBM_##X##_IS_ODE,                                            \
                                        {MBM_##X##_F_RHS, MBM_##X##_F_JAC, MBM_##X##_F_DT,           \
                                         MBM_##X##_F_FACTOR, MBM_##X##_F_SOLVE},                     \
-                                       mb_launch_##X, nullptr};                                     \
+                                       mb_launch_##X, MBM_##X##_NOBS, mb_launch_obs_##X, nullptr};                                     \
   namespace {                                                                                       \
   struct MbReg_##X {                                                                                \
     MbReg_##X() { mb_register_model(&mb_entry_##X); }                                               \

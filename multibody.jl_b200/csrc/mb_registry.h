@@ -9,6 +9,8 @@ struct MbKernelEntry {
   long long flops[5];   // rhs, jac, dT, factor, solve (algorithmic)
   // launches the ensemble kernel for `alg` on `stream`; grid sized to fill the device
   cudaError_t (*launch)(int alg, const MbArgs& args, int sm_count, cudaStream_t stream);
+  int nobs;             // observed (eliminated) variables the generated code can evaluate
+  cudaError_t (*launch_observed)(const MbObsArgs& args, int sm_count, cudaStream_t stream);
   const MbKernelEntry* next;
 };
 void mb_register_model(MbKernelEntry* e);

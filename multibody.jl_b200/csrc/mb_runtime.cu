@@ -383,6 +383,54 @@ extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, co
   return MBB200_OK;
 }
 
+// Observed (eliminated) variables of saved states, host buffers: what `sol(t, idxs = expr)` does
+// after the reference's solve (test/test_robot.jl:321-325).
+extern "C" int mbb200_model_observed_count(const mbb200_model* m, int32_t* nobs) {
+  if (!m || !nobs) return fail(MBB200_ERR_BAD_ARG, "null argument");
+  *nobs = m->entry->nobs;
+  return MBB200_OK;
+}
+
+extern "C" int mbb200_observed(mbb200_model* m, int64_t N, const double* u, const double* p, const double* saveat,
+                               int32_t n_save, double* out_obs) {
+  if (!m) return fail(MBB200_ERR_BAD_ARG, "null model");
+  if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
+  const int n = m->entry->n, mp = m->entry->m, nobs = m->entry->nobs;
+  if (nobs == 0) return fail(MBB200_ERR_UNSUPPORTED, "model '%s' has no observed variables", m->entry->name);
+  if (N < 0 || n_save < 0) return fail(MBB200_ERR_BAD_ARG, "negative size");
+  if (N == 0 || n_save == 0) return MBB200_OK;
+  if (!u || !saveat || !out_obs || (mp > 0 && !p)) return fail(MBB200_ERR_BAD_ARG, "null buffer");
+  Device& d = g_dev[0];
+  CU(cudaSetDevice(d.ordinal));
+  // processed in slabs of save points so the workspace stays bounded
+  const size_t per_save = (size_t)N * (n + nobs) * sizeof(double);
+  int slab = (int)((size_t(1) << 30) / (per_save ? per_save : 1));
+  if (slab < 1) slab = 1;
+  if (slab > n_save) slab = n_save;
+  const size_t bytes = (size_t)slab * per_save + (size_t)N * mp * sizeof(double) + (size_t)(n_save + 32) * sizeof(double);
+  int rc = ws_reserve(d, bytes);
+  if (rc) return rc;
+  double* d_u = (double*)d.ws.ptr;
+  double* d_o = d_u + (size_t)slab * N * n;
+  double* d_p = d_o + (size_t)slab * N * nobs;
+  double* d_sv = d_p + (size_t)N * mp;
+  if (mp > 0) CU(cudaMemcpyAsync(d_p, p, (size_t)N * mp * sizeof(double), cudaMemcpyHostToDevice, d.stream));
+  CU(cudaMemcpyAsync(d_sv, saveat, (size_t)n_save * sizeof(double), cudaMemcpyHostToDevice, d.stream));
+  d.last_launches = 0;
+  for (int s0 = 0; s0 < n_save; s0 += slab) {
+    const int ns = (n_save - s0 < slab) ? n_save - s0 : slab;
+    CU(cudaMemcpyAsync(d_u, u + (size_t)s0 * n * N, (size_t)ns * n * N * sizeof(double), cudaMemcpyHostToDevice, d.stream));
+    MbObsArgs a;
+    a.N = N; a.n_save = ns; a.u = d_u; a.p = d_p; a.tb = m->d_tables[0]; a.saveat = d_sv + s0; a.out = d_o;
+    cudaError_t e = m->entry->launch_observed(a, d.sm_count, d.stream);
+    if (e != cudaSuccess) return fail(MBB200_ERR_CUDA, "observed kernel launch failed: %s", cudaGetErrorString(e));
+    d.last_launches++;
+    CU(cudaMemcpyAsync(out_obs + (size_t)s0 * nobs * N, d_o, (size_t)ns * nobs * N * sizeof(double), cudaMemcpyDeviceToHost, d.stream));
+  }
+  CU(cudaStreamSynchronize(d.stream));
+  return MBB200_OK;
+}
+
 extern "C" int mbb200_last_timing(int dev_index, double* kernel_ms, int32_t* n_launches) {
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index %d", dev_index);
   if (kernel_ms) *kernel_ms = g_dev[dev_index].last_ms;

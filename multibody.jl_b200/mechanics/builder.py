@@ -41,6 +41,11 @@ class ReducedSystem:
     def m(self) -> int:
         return len(self.param_names)
 
+    @property
+    def observed_names(self) -> List[str]:
+        """Order of the generated `mbm_<model>_observed` outputs."""
+        return sorted(self.observed)
+
     def state_index(self, name: str) -> int:
         return self.state_names.index(name)
 

@@ -157,6 +157,13 @@ def robot6dof() -> ReducedSystem:
         vC = mb.state(f"axis{i+1}.motor.C.v", 0.0)
         x = mb.state(f"axis{i+1}.controller.PI.x", 0.0)
         # Controller (:207-216): e = ratio qd_ref + kp (ratio q_ref - phi_m) - w_m
+        # observed (eliminated) variables the reference's tests read through symbolic indexing
+        # (test/test_robot.jl:320-325): axisControlBus.angle_ref, .angle = motor angle / ratio
+        # (robot_components.jl:134,181), and their difference
+        mb.observed[f"pathPlanning.controlBus.axisControlBus{i+1}.angle_ref"] = q_ref.n
+        ang = phim / ratio if typ == 1 else phi[i]
+        mb.observed[f"pathPlanning.controlBus.axisControlBus{i+1}.angle"] = _node(mb, ang)
+        mb.observed[f"axis{i+1}.control_error"] = _node(mb, q_ref - ang)
         e = ratio * qd_ref + kp[i] * (ratio * q_ref - phim) - wmot
         i_ref = ks[i] * (x + e)                                      # Blocks.PI: y = k (x + e)
         mb.set_rhs(x, e / Ts[i])                                     # D(x) = e / T
@@ -172,5 +179,11 @@ def robot6dof() -> ReducedSystem:
         else:
             # rigid gear: joint torque = ratio (k i - J ratio qdd)
             joints[i].joint["tau"] = ratio * (k * cur - J * ratio * joints[i].acc)
+    for c in range(3):                                               # tool flange position in the world
+        mb.observed[f"mechanics.b6.frame_b.r_0[{c+1}]"] = _node(mb, fr.r0[c])
     mech.solve_accelerations()
     return mb.finish(tspan=(0.0, 2.0), mechanism=mech)
+
+
+def _node(mb, e):
+    return e.n if hasattr(e, "n") else mb.const(float(e)).n

@@ -30,6 +30,9 @@ def pendulum() -> ReducedSystem:
     w = mb.state("joint.w", 0.0)
     jb = mech.revolute(mech.world(), (0, 0, 1), phi, w, tau_applied=-d * w, name="joint")
     mech.body(jb, m, (0.5, 0.0, 0.0))            # I_33 = 0.001 default (components.jl:345-351)
+    tip = mech.fixed_translation(jb, (0.5, 0.0, 0.0))
+    for c in range(2):
+        mb.observed[f"body.r_0[{c+1}]"] = tip.r0[c].n    # centre of mass in the world (get_trans, orientation.jl:411)
     mech.solve_accelerations()
     mb.observed["damper.power"] = (d * w * w).n   # sensors.jl:159-173 sign aside; used by tests
     return mb.finish(tspan=(0.0, 10.0), mechanism=mech)
@@ -172,6 +175,8 @@ def rope(n_links: int = 6, name: str = "rope6") -> ReducedSystem:
         if i < n_links:
             fr = mech.body_shape(fr, tuple(li * dirv), mi, air_resistance=air)
     mech.body(fr, m_body, (0.0, 0.0, 0.0))
+    for c in range(3):
+        mb.observed[f"body.r_0[{c+1}]"] = fr.r0[c].n      # rope end (what the docs animation shows)
     mech.solve_accelerations()
     return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
 

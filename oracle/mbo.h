@@ -24,11 +24,13 @@ typedef struct {
   int nlu;            /* slots of the product's generated structured LU (checked in tests only) */
   void (*factor)(const double* u, const double* p, double t, const double* tb, double c, double* LU);
   void (*solve)(const double* LU, double c, const double* p, double* b);
+  int nobs;
+  mbo_fn observed;
 } mbo_model;
 
 const mbo_model* mbo_find_model(const char* name);
 int mbo_model_dims(const char* name, int* n, int* m, int* nnz);
-int mbo_eval(const char* name, int what /*0 rhs,1 jac(nnz),2 dT*/, const double* u, const double* p, double t, const double* tb, double* out);
+int mbo_eval(const char* name, int what /*0 rhs,1 jac(nnz),2 dT,3 observed*/, const double* u, const double* p, double t, const double* tb, double* out);
 int mbo_factor_solve(const char* name, const double* u, const double* p, double t, const double* tb, double c, double* b);
 int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass);
 int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, const double* p, const double* tb,

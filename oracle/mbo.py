@@ -50,7 +50,7 @@ def dims(model):
 
 def eval_fn(model, what, u, p, t, tb):
     n, m, nnz = dims(model)
-    out = np.zeros({0: n, 1: nnz, 2: n}[what])
+    out = np.zeros({0: n, 1: nnz, 2: n, 3: max(lib().mbo_nobs(model.encode()), 1)}[what])
     u = np.ascontiguousarray(u, dtype=np.float64); p = np.ascontiguousarray(p, dtype=np.float64)
     tb = np.ascontiguousarray(tb, dtype=np.float64)
     lib().mbo_eval(model.encode(), what, _dp(u), _dp(p), C.c_double(t), _dp(tb), _dp(out))

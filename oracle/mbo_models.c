@@ -20,8 +20,12 @@ int mbo_model_dims(const char* name, int* n, int* m, int* nnz) {
 int mbo_eval(const char* name, int what, const double* u, const double* p, double t, const double* tb, double* out) {
   const mbo_model* md = mbo_find_model(name);
   if (!md) return -1;
-  (what == 0 ? md->rhs : what == 1 ? md->jac : md->dT)(u, p, t, tb, out);
+  (what == 0 ? md->rhs : what == 1 ? md->jac : what == 2 ? md->dT : md->observed)(u, p, t, tb, out);
   return 0;
+}
+int mbo_nobs(const char* name) {
+  const mbo_model* md = mbo_find_model(name);
+  return md ? md->nobs : -1;
 }
 int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass) {
   const mbo_model* md = mbo_find_model(name);

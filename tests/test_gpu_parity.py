@@ -117,3 +117,26 @@ def test_full_size_properties_c4_sample():
     for a in range(6):
         end = sol.state(f"mechanics.r{a+1}.phi")[-1]
         assert np.abs(end - q1[a]).max() < 0.01
+
+
+def test_observed_variables_match_the_oracle_and_the_reference_assertion(oracle):
+    """`sol(tv, idxs = angle_ref - angle)`: max |control error| of axis 1 < 0.01 on 0:0.1:2 at the
+    reference's default tolerances (test/test_robot.jl:320-325), evaluated on the device; every
+    observed value equals the CPU evaluation of the same generated expression."""
+    sys_ = api.multibody("robot6dof")
+    prob = api.ODEProblem(sys_, tspan=(0.0, 2.0))
+    sv = np.linspace(0.0, 2.0, 21)
+    sol = api.solve(api.EnsembleProblem(prob), api.Rodas5P(autodiff=False), api.EnsembleB200(), trajectories=3, saveat=sv)
+    assert api.successful_retcode(sol)
+    obs = sol.observed()
+    ref = obs["pathPlanning.controlBus.axisControlBus1.angle_ref"]
+    assert not np.all(ref == 0)
+    assert np.abs(obs["axis1.control_error"]).max() < 0.01
+    names = sys_.observed_names
+    tb = sys_.tables.pack()
+    for k in (0, 7, 20):
+        want = oracle.eval_fn("robot6dof", 3, sol.u[k, :, 1], sol.p[:, 1], sv[k], tb)
+        got = np.array([obs[nm][k, 1] for nm in names])
+        np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-13)
+    with pytest.raises(KeyError):
+        sol.observed("no.such.variable")

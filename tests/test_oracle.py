@@ -212,3 +212,26 @@ def test_failure_codes(oracle):
     assert (r["retcode"] == 4).all() and np.isnan(r["u"][-1]).all()
     r = _solve(oracle, spec, dtmin=1.0)
     assert (r["retcode"] == 5).all()
+
+
+def test_observed_expressions(oracle):
+    """Observed (eliminated) variables: robot tool position from an independent forward
+    kinematics; pendulum body position on the unit circle of radius 0.5."""
+    from ref_models import rodrigues, AXES_N, LINKS, BASE_R
+    sysm = get_model("robot6dof")
+    names = sysm.observed_names
+    rng = np.random.default_rng(11)
+    u = sysm.u0 + 0.4 * rng.normal(size=36)
+    got = oracle.eval_fn("robot6dof", 3, u, sysm.p0, 0.7, sysm.tables.pack())
+    T, p = np.eye(3), BASE_R.copy()
+    for i in range(6):
+        T = T @ rodrigues(AXES_N[i], u[2 * i])
+        p = p + T @ np.array(LINKS[i][0], float)
+    tool = [got[names.index(f"mechanics.b6.frame_b.r_0[{c+1}]")] for c in range(3)]
+    np.testing.assert_allclose(tool, p, atol=1e-12)
+    assert got[names.index("pathPlanning.controlBus.axisControlBus1.angle")] == pytest.approx(
+        u[sysm.state_index("axis1.motor.Jmotor.phi")] / -105.0)
+    pen = get_model("pendulum")
+    o = oracle.eval_fn("pendulum", 3, np.array([0.3, 1.0]), pen.p0, 0.0, pen.tables.pack())
+    x, y = o[pen.observed_names.index("body.r_0[1]")], o[pen.observed_names.index("body.r_0[2]")]
+    np.testing.assert_allclose([x, y], [0.5 * np.cos(0.3), 0.5 * np.sin(0.3)], atol=1e-14)
