@@ -220,10 +220,21 @@ def main():
     ftraj, f_step, dense_step, steps = flops_per_trajectory(flops, n, ns, stats, spec.alg)
     peak = _lib.measure_fp64_peak(0)
     achieved = float(ftraj.sum()) * args.steps / (dev_ms * 1e-3)
-    traffic = None
+    # DRAM bytes of the dominant kernel per launch: ncu-measured bytes per trajectory (one
+    # `--set full` capture, profiles/traffic.json) x trajectories of this launch
+    traffic, hbm = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(spec.config)
+        tj = json.load(open(tpath)).get(spec.config)
+        if tj:
+            traffic = tj["dram_bytes_per_trajectory"] * N
+            peak_hbm = 6530.6
+            ppath = os.path.join(ROOT, "MEASURED_PEAKS.json")
+            if os.path.exists(ppath):
+                peak_hbm = json.load(open(ppath)).get("hbm_gbs", peak_hbm)
+            gbs = traffic * args.steps / (dev_ms * 1e-3) / 1e9
+            hbm = {"achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm,
+                   "note": "thread-local working state spilling past the 126 MB L2 (not algorithmic traffic)"}
 
     # ---- end to end through the host-buffer ABI call (pinned host memory) ----------------------
     h_u0 = torch.from_numpy(spec.u0).pin_memory()
@@ -273,7 +284,8 @@ def main():
                      "frac": achieved / peak, "traffic": traffic,
                      "peak_source": "FP64 DFMA probe measured in this run (MEASURED_PEAKS.json holds HBM/BF16 only)",
                      "flops_per_step_structured": f_step, "flops_per_step_dense_equiv": dense_step,
-                     "hbm_gbs_algorithmic": (h2d + d2h) * args.steps / (dev_ms * 1e-3) / 1e9},
+                     "hbm_gbs_algorithmic": (h2d + d2h) * args.steps / (dev_ms * 1e-3) / 1e9,
+                     "dram_measured": hbm},
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         # the oracle on the host cores, in a fresh interpreter (no torch/OpenMP worker threads
