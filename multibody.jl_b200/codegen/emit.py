@@ -28,6 +28,12 @@ class Printer:
         self.scheduled = scheduled
         self.input_fmt = input_fmt
         self.interp_fmt = interp_fmt
+        # staged spilling: when > 0, `function` keeps at most `reg_target` temporaries in named
+        # variables and parks the ones with the farthest next use in MB_S(slot) (shared memory
+        # on the GPU), instead of leaving the choice -- and a trip to DRAM -- to ptxas
+        self.smem_slots = 0
+        self.reg_target = 72
+        self._alias: Dict[int, str] = {}
         self._seg: Dict[int, str] = {}        # time node -> name of its table-segment variable
         self._paired: Dict[int, int] = {}     # sin/cos node -> partner emitted in the same MB_SINCOS
         self._emitted: set = set()
@@ -36,6 +42,7 @@ class Printer:
         """Per-function state: table segments already located, sin/cos pairs of one argument."""
         g = self.g
         self._seg, self._paired, self._emitted = {}, {}, set()
+        self._alias = {}
         by_arg: Dict[int, Dict[int, int]] = {}
         for n in order:
             if g.op[n] in (SIN, COS):
@@ -56,7 +63,7 @@ class Printer:
             return self.input_fmt[kind].format(i=idx)
         if o == NEG:
             return f"(-{self.ref(g.a[n])})"
-        return f"x{n}"
+        return self._alias.get(n) or f"x{n}"
 
     def _line(self, n: int, indent: str):
         g = self.g
@@ -129,18 +136,84 @@ class Printer:
                 lines.append(f"{indent}{lhs} = {self.ref(n)};")
         else:
             order = g.schedule([n for _, n in assigns])
-            pos = {n: i for i, n in enumerate(order)}
             by_node: Dict[int, List[str]] = {}
             for lhs, n in assigns:
                 by_node.setdefault(n, []).append(lhs)
             emitted_lhs = set()
-            for n in order:
+            stage = self.smem_slots > 0
+            if stage:
+                import bisect
+                trivial = (CONST, INPUT, NEG)
+
+                def operands(n):
+                    o = g.op[n]
+                    if o in (CONST, INPUT):
+                        return []
+                    ks = [g.a[n]]
+                    if o in (ADD, SUB, MUL, DIV, ATAN2, MIN, MAX):
+                        ks.append(g.b[n])
+                    elif o == SELGE:
+                        ks += [g.b[n], g.c[n]]
+                    out = []
+                    for k in ks:
+                        while g.op[k] == NEG:
+                            k = g.a[k]
+                        if g.op[k] not in (CONST, INPUT):
+                            out.append(k)
+                    return out
+                uses: Dict[int, List[int]] = {}
+                for i, n in enumerate(order):
+                    if g.op[n] in trivial:
+                        continue
+                    for k in operands(n):
+                        uses.setdefault(k, []).append(i)
+
+                def next_use(k, i):
+                    u = uses.get(k, ())
+                    j = bisect.bisect_right(u, i)
+                    return u[j] if j < len(u) else None
+                live: set = set()
+                slot_of: Dict[int, int] = {}
+                free = list(range(self.smem_slots - 1, -1, -1))
+                nreload = 0
+                lines.append(f"{indent}MB_S_DECL")
+            for i, n in enumerate(order):
+                if stage and g.op[n] not in (CONST, INPUT, NEG) and n not in self._emitted:
+                    for k in operands(n):                     # bring parked operands back
+                        if k not in live and k in slot_of:
+                            nreload += 1
+                            nm = f"x{k}_r{nreload}"
+                            lines.append(f"{indent}const double {nm} = MB_S({slot_of[k]});")
+                            self._alias[k] = nm
+                            live.add(k)
                 ln = self._line(n, indent)
                 if ln is not None:
                     lines.append(ln)
                 for lhs in by_node.get(n, ()):
                     lines.append(f"{indent}{lhs} = {self.ref(n)};")
                     emitted_lhs.add(lhs)
+                if stage and g.op[n] not in (CONST, INPUT, NEG):
+                    if ln is not None:
+                        for d_ in (n, self._paired.get(n)):
+                            if d_ is not None and next_use(d_, i) is not None:
+                                live.add(d_)
+                    for k in list(live):                      # values that are dead from here on
+                        if next_use(k, i) is None:
+                            live.discard(k)
+                            if k in slot_of:
+                                free.append(slot_of.pop(k))
+                    nxt = set(operands(order[i + 1])) if i + 1 < len(order) else set()
+                    while len(live) > self.reg_target:
+                        cand = [k for k in live if k not in nxt]
+                        if not cand:
+                            break
+                        v = max(cand, key=lambda k: next_use(k, i))
+                        if v not in slot_of:
+                            if not free:
+                                break
+                            slot_of[v] = free.pop()
+                            lines.append(f"{indent}MB_S({slot_of[v]}) = {self.ref(v)};")
+                        live.discard(v)
             for lhs, n in assigns:          # outputs that are constants / inputs
                 if lhs not in emitted_lhs:
                     lines.append(f"{indent}{lhs} = {self.ref(n)};")

@@ -230,6 +230,8 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(f"#define MBM_{X}_F_SOLVE {code.F_solve}")
     obs_names = sorted(sys.observed)
     out.append(f"#define MBM_{X}_NOBS {len(obs_names)}")
+    slots = int(sys.meta.get("smem_slots", 0))
+    out.append(f"#define MBM_{X}_SMEM_SLOTS {slots}")
     out.append(f"#define MBM_{X}_HAS_DT {1 if any(d != g.zero for d in code.dT_nodes) else 0}")
     out.append(f"#define MBM_{X}_IS_ODE {1 if all(sys.mass_diag) else 0}")
     out.append("#ifndef MB_NO_PATTERN")
@@ -249,8 +251,10 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append("  return (int)((w[i >> 6] >> (i & 63)) & 1ull);")
     out.append("}")
     out.append("")
+    pr.smem_slots, pr.reg_target = slots, int(sys.meta.get("reg_target", 72))
     out.append(pr.function(f"MB_FN_RHS void mbm_{X}_rhs({args}, double* MB_RESTRICT du)",
                            [(f"du[{i}]", sys.rhs[i]) for i in range(n)]))
+    pr.smem_slots = 0
     out.append("")
     out.append(pr.function(f"MB_FN void mbm_{X}_jac({args}, double* MB_RESTRICT Jnz)",
                            [(f"Jnz[{k}]", e[2]) for k, e in enumerate(code.jac_entries)]))
@@ -262,10 +266,12 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(pr.function(f"MB_FN void mbm_{X}_observed({args}, double* MB_RESTRICT obs)",
                            [(f"obs[{k}]", sys.observed[nm]) for k, nm in enumerate(obs_names)]))
     out.append("")
+    pr.smem_slots = slots if sys.meta.get("stage_factor", True) else 0
     lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)]
     out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     out.append("")
+    pr.smem_slots = 0
     spr = Printer(code.solve_graph, {"lu": "LU[{i}]", "b": "b{i}", "c": "c", "p": "p[{i}]"})
     sol_lines = [f"MB_FN_SOLVE void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "
                  f"double* MB_RESTRICT b) {{"]

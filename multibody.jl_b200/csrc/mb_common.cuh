@@ -55,6 +55,11 @@ __device__ __forceinline__ double mb_tab(const MbSeg& sg, int table) {
 #define MB_TAB_LINEAR2(tb, sg, k) mb_tab<2>(sg, k)
 #define MB_TAB_LINEAR3(tb, sg, k) mb_tab<3>(sg, k)
 #define MB_SINCOS(x, s, c) sincos(x, &(s), &(c))
+// staged temporaries of the generated code (codegen/emit.py): slot k of this thread, in dynamic
+// shared memory laid out [slot][thread] (conflict-free); MB_S_STRIDE = threads per CTA of the TU
+extern __shared__ double mb_dyn_smem[];
+#define MB_S_DECL
+#define MB_S(k) ((volatile double*)mb_dyn_smem)[(k) * MB_S_STRIDE + threadIdx.x]   // volatile: no store-to-load forwarding back into registers
 
 // ---- method coefficients (published methods) ------------------------
 // __constant__ tables: indices are warp-uniform, so every read is a constant-bank broadcast.

@@ -69,24 +69,27 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
   };                                                                                                \
   static cudaError_t mb_launch_##X(int alg, const MbArgs& a, int sm_count, cudaStream_t st) {       \
     int bps = 1;                                                                                    \
+    const size_t smem = (size_t)MBM_##X##_SMEM_SLOTS * sizeof(double) * BLOCK;                      \
     if (alg == 1) {                                                                                 \
       auto kern = mbk::ensemble_kernel<MbModel_##X, 1, BLOCK, MINB, UNR>;                           \
-      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 0);                \
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, 0);                          \
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \
       bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
       long long need = (a.N + BLOCK - 1) / BLOCK;                                                   \
       if (grid > need) grid = need;                                                                 \
-      kern<<<(unsigned)grid, BLOCK, 0, st>>>(a);                                                    \
+      kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 2) {                                                                          \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, BLOCK, MINB, UNR);                                   \
-      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 0);                \
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, 0);                          \
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \
       bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
       long long need = (a.N + BLOCK - 1) / BLOCK;                                                   \
       if (grid > need) grid = need;                                                                 \
-      kern<<<(unsigned)grid, BLOCK, 0, st>>>(a);                                                    \
+      kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else {                                                                                        \
       return cudaErrorInvalidValue;                                                                 \
     }                                                                                               \

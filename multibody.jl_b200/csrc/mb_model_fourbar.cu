@@ -4,5 +4,6 @@
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__
 #define MB_NO_PATTERN
+#define MB_S_STRIDE 128
 #include "generated/mbm_fourbar.h"
 MB_DEFINE_MODEL(fourbar, 128, 1, 0)

@@ -15,10 +15,11 @@
 #ifndef MB_R_UNR
 #define MB_R_UNR 0
 #endif
-#include "generated/mbm_robot6dof.h"
 #ifndef MB_R_BLOCK
 #define MB_R_BLOCK 256
 #endif
+#define MB_S_STRIDE MB_R_BLOCK
+#include "generated/mbm_robot6dof.h"
 #ifndef MB_R_MINB
 #define MB_R_MINB 1
 #endif

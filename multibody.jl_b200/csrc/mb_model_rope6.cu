@@ -3,5 +3,6 @@
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__
 #define MB_NO_PATTERN
+#define MB_S_STRIDE 128
 #include "generated/mbm_rope6.h"
 MB_DEFINE_MODEL(rope6, 128, 1, 0)

@@ -182,7 +182,15 @@ def robot6dof() -> ReducedSystem:
     for c in range(3):                                               # tool flange position in the world
         mb.observed[f"mechanics.b6.frame_b.r_0[{c+1}]"] = _node(mb, fr.r0[c])
     mech.solve_accelerations()
-    return mb.finish(tspan=(0.0, 2.0), mechanism=mech)
+    import os
+    # staged temporaries (codegen/emit.py): tuning knobs of the emitted kernels, not of the model.
+    # Measured on B200 (profiles/r01_robot_v5_summary.md): parking long-lived temporaries in shared
+    # memory removes 45 % of the local accesses of rhs() but runs 12 % slower (volatile LDS in the
+    # dependency chains, 2 warps per scheduler), so it is off (0 slots) by default.
+    return mb.finish(tspan=(0.0, 2.0), mechanism=mech,
+                     smem_slots=int(os.environ.get("MB_ROBOT_SLOTS", "0")),
+                     reg_target=int(os.environ.get("MB_ROBOT_RTARGET", "72")),
+                     stage_factor=os.environ.get("MB_ROBOT_STAGE_FACTOR", "1") == "1")
 
 
 def _node(mb, e):

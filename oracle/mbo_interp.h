@@ -52,5 +52,8 @@ static inline double mbo_interp(const double* tb, int table, double t, int cubic
 #define MB_TAB_LINEAR1(tb, sg, k) mbo_interp(tb, k, sg, 0, 1)
 #define MB_TAB_LINEAR2(tb, sg, k) mbo_interp(tb, k, sg, 0, 2)
 #define MB_TAB_LINEAR3(tb, sg, k) mbo_interp(tb, k, sg, 0, 3)
+/* staged temporaries of the generated code: plain locals here (shared memory on the GPU) */
+#define MB_S_DECL double mb_s_[128];
+#define MB_S(k) mb_s_[k]
 #define MB_SINCOS(x, s, c) do { (s) = sin(x); (c) = cos(x); } while (0)
 #endif
