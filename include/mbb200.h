@@ -29,8 +29,8 @@ extern "C" {
 
 #define MBB200_ABI_VERSION 1
 
-/* algorithm ids (OrdinaryDiffEq names: Tsit5(), Rodas5P()) */
-enum { MBB200_ALG_TSIT5 = 1, MBB200_ALG_RODAS5P = 2 };
+/* algorithm ids (OrdinaryDiffEq names: Tsit5(), Rodas5P(), Rodas4()) */
+enum { MBB200_ALG_TSIT5 = 1, MBB200_ALG_RODAS5P = 2, MBB200_ALG_RODAS4 = 3 };
 
 /* SciMLBase.ReturnCode values written to retcode[] */
 enum {

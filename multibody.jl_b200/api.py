@@ -37,6 +37,14 @@ class Rodas5P:
     id: int = _lib.ALG_RODAS5P
 
 
+@dataclass(frozen=True)
+class Rodas4:
+    """The solver most of the reference's tests use (test/basic_tests.jl, 25 call sites;
+    docs/src/examples/ropes_and_cables.md:36 `Rodas4(autodiff=false)`)."""
+    autodiff: bool = True
+    id: int = _lib.ALG_RODAS4
+
+
 @dataclass
 class EnsembleB200:
     """The new `SciMLBase.EnsembleAlgorithm`.  `devices`: CUDA ordinals used by this

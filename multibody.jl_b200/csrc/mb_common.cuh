@@ -85,7 +85,8 @@ static __constant__ double RD_H[3][8] = {
     {11.419903575922262, 2.8879645146136994, 72.92137995996029, 80.12511834622643, -52.072871366152654, -59.78993625266729, -0.15582684282751913, 4.883087185713722}};
 
 // PI step controller of the reference's integrators
-constexpr double BETA1 = 7.0 / 50.0, BETA2 = 2.0 / 25.0, SAFETY = 0.9, QMIN = 0.2, QMAX = 10.0,
+// (beta1 = 7/(10 order), beta2 = 2/(5 order) are set per method inside the kernels)
+constexpr double SAFETY = 0.9, QMIN = 0.2, QMAX = 10.0,
                  QOLDINIT = 1e-4;
 
 enum { RC_DEFAULT = 0, RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6 };

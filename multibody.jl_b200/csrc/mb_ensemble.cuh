@@ -52,6 +52,51 @@ static __constant__ double cTS_A[7][6] = {
     {0.09646076681806523, 0.01, 0.4798896504144996, 1.379008574103742, -3.290069515436081, 2.324710524099774}};
 static __constant__ double cTS_C[7] = {0.0, 0.161, 0.327, 0.9, 0.9800255409045097, 1.0, 1.0};
 
+// Rodas4 (Hairer & Wanner RODAS; OrdinaryDiffEq `Rodas4`, the solver most of the reference's
+// tests use): 6 stages, augmented a-row 5 folds "u6 = u5 + k5"
+static __constant__ double cR4_A[6][5] = {
+    {0, 0, 0, 0, 0},
+    {1.544, 0, 0, 0, 0},
+    {0.9466785280815826, 0.2557011698983284, 0, 0, 0},
+    {3.314825187068521, 2.896124015972201, 0.9986419139977817, 0, 0},
+    {1.221224509226641, 6.019134481288629, 12.53708332932087, -0.6878860361058950, 0},
+    {1.221224509226641, 6.019134481288629, 12.53708332932087, -0.6878860361058950, 1.0}};
+static __constant__ double cR4_C[6][5] = {
+    {0, 0, 0, 0, 0},
+    {-5.6688, 0, 0, 0, 0},
+    {-2.430093356833875, -0.2063599157091915, 0, 0, 0},
+    {-0.1073529058151375, -9.594562251023355, -20.47028614809616, 0, 0},
+    {7.496443313967647, -10.24680431464352, -33.99990352819905, 11.70890893206160, 0},
+    {8.083246795921522, -7.981132988064893, -31.52159432874371, 16.31930543123136, -6.058818238834054}};
+static __constant__ double cR4_CT[6] = {0.0, 0.386, 0.21, 0.63, 1.0, 1.0};
+static __constant__ double cR4_D[6] = {0.25, -0.1043, 0.1035, -0.03620000000000023, 0.0, 0.0};
+static __constant__ double cR4_H[3][6] = {
+    {10.12623508344586, -7.487995877610167, -34.80091861555747, -7.992771707568823, 1.025137723295662, 0.0},
+    {-0.6762803392801253, 6.087714651680015, 16.43084320892478, 24.76722511418386, -6.594389125716872, 0.0},
+    {0, 0, 0, 0, 0, 0}};
+
+// Rosenbrock tableaus as traits (all reads are warp-uniform constant-bank loads)
+struct TabRodas5P {
+  static constexpr int NST = 8, ORDER = 5;
+  static constexpr double GAMMA = RD_GAMMA;
+  static __device__ __forceinline__ double A(int s, int j) { return cRD_A[s][j]; }
+  static __device__ __forceinline__ double C(int s, int j) { return cRD_C[s][j]; }
+  static __device__ __forceinline__ double CT(int s) { return cRD_CT[s]; }
+  static __device__ __forceinline__ double D(int s) { return cRD_D[s]; }
+  static __device__ __forceinline__ double H(int r, int j) { return RD_H[r][j]; }
+};
+struct TabRodas4 {
+  static constexpr int NST = 6, ORDER = 4;
+  static constexpr double GAMMA = 0.25;
+  static __device__ __forceinline__ double A(int s, int j) { return cR4_A[s][j]; }
+  static __device__ __forceinline__ double C(int s, int j) { return cR4_C[s][j]; }
+  static __device__ __forceinline__ double CT(int s) { return cR4_CT[s]; }
+  static __device__ __forceinline__ double D(int s) { return cR4_D[s]; }
+  static __device__ __forceinline__ double H(int r, int j) { return cR4_H[r][j]; }
+};
+template <int ALG> struct TabOf { using type = TabRodas5P; };
+template <> struct TabOf<3> { using type = TabRodas4; };
+
 template <int N>
 __device__ __forceinline__ double scaled_rms(const double (&e)[N], const double (&ua)[N],
                                              const double (&ub)[N], double atol, double rtol) {
@@ -69,7 +114,7 @@ __device__ __forceinline__ double scaled_rms(const double (&e)[N], const double 
 // as the CPU oracle so that both start from the same first step.
 template <class M>
 __device__ __noinline__ double initial_dt(const double (&u)[M::N], const double* p, const double* tb,
-                                          double t0, double dtmax, double atol, double rtol) {
+                                          double t0, double dtmax, double atol, double rtol, int order = 5) {
   constexpr int N = M::N;
   double f0[N], u1[N], f1[N];
   M::rhs(u, p, t0, tb, f0);
@@ -98,7 +143,7 @@ __device__ __noinline__ double initial_dt(const double (&u)[M::N], const double*
   }
   d2 = sqrt(d2 / N) / dt0;
   const double dm = fmax(d1, d2);
-  const double dt1 = (dm <= 1e-15) ? fmax(1e-6, dt0 * 1e-3) : pow(10.0, -(2.0 + log10(dm)) / 5.0);
+  const double dt1 = (dm <= 1e-15) ? fmax(1e-6, dt0 * 1e-3) : pow(10.0, -(2.0 + log10(dm)) / (double)order);
   return fmin(fmin(100.0 * dt0, dt1), dtmax);
 }
 
@@ -107,13 +152,17 @@ __device__ __noinline__ double initial_dt(const double (&u)[M::N], const double*
 namespace mbk {
 
 // M supplies: N, NP, NLU, HAS_DT, rhs(), dT(), factor(), solve(), isdiff().
-// ALG: 1 = Tsit5, 2 = Rodas5P.  UNR: 1 -> stage loop fully unrolled (small models).
+// ALG: 1 = Tsit5, 2 = Rodas5P, 3 = Rodas4.  UNR: 1 -> stage loop fully unrolled (small models).
 template <class M, int ALG, int BLOCK, int MINB, int UNR>
 __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
   constexpr int N = M::N;
   constexpr int NP = (M::NP > 0 ? M::NP : 1);
-  constexpr bool ROSEN = (ALG == 2);
-  constexpr int NK = ROSEN ? 8 : 7;
+  constexpr bool ROSEN = (ALG >= 2);
+  using T = typename TabOf<ALG>::type;
+  constexpr int NST = T::NST;
+  constexpr int NK = ROSEN ? NST : 7;
+  constexpr int ORDER = ROSEN ? T::ORDER : 5;
+  constexpr double BETA1 = 7.0 / (10.0 * ORDER), BETA2 = 2.0 / (5.0 * ORDER);
   constexpr int NLU = ROSEN ? (M::NLU > 0 ? M::NLU : 1) : 1;
   constexpr int NDT = (ROSEN && M::HAS_DT) ? N : 1;
   constexpr unsigned FULL = 0xffffffffu;
@@ -150,7 +199,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
           is++;
         }
         if (a.dt0 > 0.0) dt = a.dt0;
-        else { dt = initial_dt<M>(u, p, tb, a.t0, dtmax, a.abstol, a.reltol); nf += 2; }
+        else { dt = initial_dt<M>(u, p, tb, a.t0, dtmax, a.abstol, a.reltol, ORDER); nf += 2; }
         if (!ROSEN) { M::rhs(u, p, t, tb, k[0]); nf++; }   // k[0] = f(u,t), kept across rejections
         active = true;
         if (!(t < a.t1)) rc = RC_SUCCESS;
@@ -175,19 +224,19 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
       double EEst;
       if (ROSEN) {
         // ---- Rodas5P step: W = M/(gamma dt) - J factored once, 8 stage solves ------------
-        const double cW = 1.0 / (dt * RD_GAMMA);
+        const double cW = 1.0 / (dt * T::GAMMA);
         M::factor(u, p, t, tb, cW, LU);
         njac++;
         if (M::HAS_DT) M::dT(u, p, t, tb, dT);
         const double inv_dt = 1.0 / dt;
 #pragma unroll(UNR ? 8 : 1)
-        for (int s = 0; s < 8; s++) {
+        for (int s = 0; s < NST; s++) {
           double sc[N];
 #pragma unroll
           for (int i = 0; i < N; i++) { us[i] = u[i]; sc[i] = 0.0; }
 #pragma unroll(UNR ? 8 : 1)
           for (int j = 0; j < s; j++) {
-            const double aj = cRD_A[s][j], cj = cRD_C[s][j];
+            const double aj = T::A(s, j), cj = T::C(s, j);
 #pragma unroll
             for (int i = 0; i < N; i++) {
               const double kj = k[j][i];
@@ -196,8 +245,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
             }
           }
           double r[N];
-          M::rhs(us, p, t + cRD_CT[s] * dt, tb, r);
-          const double dd = dt * cRD_D[s];
+          M::rhs(us, p, t + T::CT(s) * dt, tb, r);
+          const double dd = dt * T::D(s);
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = r[i];
@@ -209,10 +258,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
 #pragma unroll
           for (int i = 0; i < N; i++) k[s][i] = r[i];
         }
-        nf += 8; nsolve += 8;
+        nf += NST; nsolve += NST;
 #pragma unroll
-        for (int i = 0; i < N; i++) un[i] = us[i] + k[7][i];
-        EEst = scaled_rms<N>(k[7], u, un, a.abstol, a.reltol);
+        for (int i = 0; i < N; i++) un[i] = us[i] + k[NK - 1][i];
+        EEst = scaled_rms<N>(k[NK - 1], u, un, a.abstol, a.reltol);
       } else {
         // ---- Tsit5 step (FSAL: k[0] holds f(u,t); refreshed from k[6] on acceptance) -----
 #pragma unroll(UNR ? 7 : 1)
@@ -271,9 +320,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
                 for (int i = 0; i < N; i++) {
                   double K1 = 0, K2 = 0, K3 = 0;
 #pragma unroll
-                  for (int j = 0; j < 8; j++) {
+                  for (int j = 0; j < NST; j++) {
                     const double kj = k[j][i];
-                    K1 = fma(RD_H[0][j], kj, K1); K2 = fma(RD_H[1][j], kj, K2); K3 = fma(RD_H[2][j], kj, K3);
+                    K1 = fma(T::H(0, j), kj, K1); K2 = fma(T::H(1, j), kj, K2); K3 = fma(T::H(2, j), kj, K3);
                   }
                   o[(size_t)i * a.N] = (1.0 - th) * u[i] + th * (un[i] + (1.0 - th) * (K1 + th * (K2 + th * K3)));
                 }

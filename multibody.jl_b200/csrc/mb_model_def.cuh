@@ -36,9 +36,10 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 
 // MB_RODAS_CLASSIC selects the first Rodas5P kernel (vectors as separate local arrays)
 #ifdef MB_RODAS_CLASSIC
-#define MB_RODAS_KERNEL(MODEL, BLOCK, MINB, UNR) mbk::ensemble_kernel<MODEL, 2, BLOCK, MINB, UNR>
+#define MB_RODAS_KERNEL(MODEL, ALG, BLOCK, MINB, UNR) mbk::ensemble_kernel<MODEL, ALG, BLOCK, MINB, UNR>
 #else
-#define MB_RODAS_KERNEL(MODEL, BLOCK, MINB, UNR) mbk::rodas5p_rows_kernel<MODEL, BLOCK, MINB>
+#define MB_RODAS_KERNEL(MODEL, ALG, BLOCK, MINB, UNR) \
+  mbk::rosenbrock_rows_kernel<MODEL, typename mbk::TabOf<ALG>::type, BLOCK, MINB>
 #endif
 
 #define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
@@ -81,7 +82,17 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 2) {                                                                          \
-      auto kern = MB_RODAS_KERNEL(MbModel_##X, BLOCK, MINB, UNR);                                   \
+      auto kern = MB_RODAS_KERNEL(MbModel_##X, 2, BLOCK, MINB, UNR);                                   \
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \
+      bps = mb_cap_ctas_per_sm(bps);                                                                \
+      long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
+      long long need = (a.N + BLOCK - 1) / BLOCK;                                                   \
+      if (grid > need) grid = need;                                                                 \
+      kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
+    } else if (alg == 3) {                                                                          \
+      auto kern = MB_RODAS_KERNEL(MbModel_##X, 3, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \

@@ -1,4 +1,4 @@
-// Rodas5P ensemble kernel, "row workspace" variant.
+// Rosenbrock (Rodas5P / Rodas4) ensemble kernel, "row workspace" variant.
 //
 // Same algorithm and arithmetic as the Rodas5P branch of mbk::ensemble_kernel
 // (mb_ensemble.cuh); what differs is where the per-trajectory vectors live.  Every vector
@@ -13,12 +13,13 @@
 
 namespace mbk {
 
-template <class M, int BLOCK, int MINB>
-__global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs a) {
-  constexpr int N = M::N;
+template <class M, class T, int BLOCK, int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbArgs a) {
+  constexpr int N = M::N, NST = T::NST;
+  constexpr double BETA1 = 7.0 / (10.0 * T::ORDER), BETA2 = 2.0 / (5.0 * T::ORDER);
   constexpr int NPR = (M::NP + N - 1) / N > 0 ? (M::NP + N - 1) / N : 1;
   constexpr int NLUR = (M::NLU + N - 1) / N > 0 ? (M::NLU + N - 1) / N : 1;
-  constexpr int R_US = 8, R_SC = 9, R_U = 10, R_DT = 11, R_P = 12, R_LU = R_P + NPR, ROWS = R_LU + NLUR;
+  constexpr int R_US = NST, R_SC = NST + 1, R_U = NST + 2, R_DT = NST + 3, R_P = NST + 4, R_LU = R_P + NPR, ROWS = R_LU + NLUR;
   constexpr unsigned FULL = 0xffffffffu;
   constexpr double EPS = 2.220446049250313e-16;
 
@@ -60,7 +61,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs 
         }
         if (a.dt0 > 0.0) dt = a.dt0;
         else {
-          dt = initial_dt<M>(*reinterpret_cast<const double(*)[N]>(u), p, tb, a.t0, dtmax, a.abstol, a.reltol);
+          dt = initial_dt<M>(*reinterpret_cast<const double(*)[N]>(u), p, tb, a.t0, dtmax, a.abstol, a.reltol, T::ORDER);
           nf += 2;
         }
         active = true;
@@ -77,20 +78,20 @@ __global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs 
     if (active && rc == RC_DEFAULT) {
       bool last = false;
       if (t + dt >= a.t1 - 100.0 * EPS * fabs(a.t1)) { dt = a.t1 - t; last = true; }
-      const double cW = 1.0 / (dt * RD_GAMMA);
+      const double cW = 1.0 / (dt * T::GAMMA);
       M::factor(u, p, t, tb, cW, LU);
       njac++;
       if (M::HAS_DT) M::dT(u, p, t, tb, dT);
       const double inv_dt = 1.0 / dt;
 #pragma unroll 1
-      for (int s = 0; s < 8; s++) {
+      for (int s = 0; s < NST; s++) {
         {
           double x[N], y[N];
 #pragma unroll
           for (int i = 0; i < N; i++) { x[i] = u[i]; y[i] = 0.0; }
 #pragma unroll 1
           for (int j = 0; j < s; j++) {
-            const double aj = cRD_A[s][j], cj = cRD_C[s][j];
+            const double aj = T::A(s, j), cj = T::C(s, j);
 #pragma unroll
             for (int i = 0; i < N; i++) {
               const double kj = W[j][i];
@@ -101,10 +102,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs 
 #pragma unroll
           for (int i = 0; i < N; i++) { us[i] = x[i]; sc[i] = y[i]; }
         }
-        M::rhs(us, p, t + cRD_CT[s] * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
+        M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
         {
           double r[N];
-          const double dd = dt * cRD_D[s];
+          const double dd = dt * T::D(s);
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = W[s][i];
@@ -117,14 +118,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs 
           for (int i = 0; i < N; i++) W[s][i] = r[i];
         }
       }
-      nf += 8; nsolve += 8;
+      nf += NST; nsolve += NST;
       // u_new = us + k8; error estimate = k8
       double EEst;
       {
         double sacc = 0.0;
 #pragma unroll
         for (int i = 0; i < N; i++) {
-          const double k8 = W[7][i], ua = u[i], ub = us[i] + k8;
+          const double k8 = W[NST - 1][i], ua = u[i], ub = us[i] + k8;
           const double scl = a.abstol + fmax(fabs(ua), fabs(ub)) * a.reltol;
           const double q = k8 / scl;
           sacc += q * q;
@@ -149,24 +150,24 @@ __global__ void __launch_bounds__(BLOCK, MINB) rodas5p_rows_kernel(const MbArgs 
             double* __restrict__ o = a.out_u + (size_t)is * N * a.N + traj;
             if (ts == tn) {
 #pragma unroll
-              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = us[i] + W[7][i];
+              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = us[i] + W[NST - 1][i];
             } else {
               const double th = (ts - t) / dt;
               for (int i = 0; i < N; i++) {
                 double K1 = 0, K2 = 0, K3 = 0;
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
+                for (int j = 0; j < NST; j++) {
                   const double kj = W[j][i];
-                  K1 = fma(RD_H[0][j], kj, K1); K2 = fma(RD_H[1][j], kj, K2); K3 = fma(RD_H[2][j], kj, K3);
+                  K1 = fma(T::H(0, j), kj, K1); K2 = fma(T::H(1, j), kj, K2); K3 = fma(T::H(2, j), kj, K3);
                 }
-                const double un = us[i] + W[7][i];
+                const double un = us[i] + W[NST - 1][i];
                 o[(size_t)i * a.N] = (1.0 - th) * u[i] + th * (un + (1.0 - th) * (K1 + th * (K2 + th * K3)));
               }
             }
             is++;
           }
 #pragma unroll
-          for (int i = 0; i < N; i++) u[i] = us[i] + W[7][i];
+          for (int i = 0; i < N; i++) u[i] = us[i] + W[NST - 1][i];
           t = tn;
           qold = fmax(EEst, QOLDINIT);
           dt = fmin(dt / q, dtmax);

@@ -260,9 +260,9 @@ __global__ void __launch_bounds__(256) mb_reduce_kernel(const double* __restrict
 static int check_opts(const mbb200_model* m, const mbb200_opts* o, long long N, int n_save) {
   if (!m || !o) return fail(MBB200_ERR_BAD_ARG, "null model or options");
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
-  if (o->alg != MBB200_ALG_TSIT5 && o->alg != MBB200_ALG_RODAS5P) return fail(MBB200_ERR_BAD_ARG, "unknown algorithm id %d", o->alg);
+  if (o->alg != MBB200_ALG_TSIT5 && o->alg != MBB200_ALG_RODAS5P && o->alg != MBB200_ALG_RODAS4) return fail(MBB200_ERR_BAD_ARG, "unknown algorithm id %d", o->alg);
   if (o->alg == MBB200_ALG_TSIT5 && !m->entry->is_ode)
-    return fail(MBB200_ERR_UNSUPPORTED, "Tsit5 needs an explicit ODE; model '%s' has a singular mass matrix (use Rodas5P)", m->entry->name);
+    return fail(MBB200_ERR_UNSUPPORTED, "Tsit5 needs an explicit ODE; model '%s' has a singular mass matrix (use Rodas5P or Rodas4)", m->entry->name);
   if (N < 0 || n_save < 0) return fail(MBB200_ERR_BAD_ARG, "negative size");
   if (!(o->abstol > 0.0) || !(o->reltol > 0.0)) return fail(MBB200_ERR_BAD_ARG, "abstol and reltol must be positive");
   if (!(o->t1 >= o->t0)) return fail(MBB200_ERR_BAD_ARG, "tspan must be increasing");

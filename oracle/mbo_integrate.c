@@ -25,6 +25,28 @@
 /* SciMLBase.ReturnCode values */
 enum { RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6 };
 
+/* Rosenbrock tableau in the transformed (Hairer-Wanner) form, padded to 8 stages */
+typedef struct {
+  int nst, nexp;          /* stages; stages 0..nexp-1 use rows of A, the rest add the previous k */
+  int order;
+  double gamma;
+  double A[8][7], C[8][7], CT[8], D[8], H[3][8];
+} rosen_tab;
+static void rosen_get(int alg, rosen_tab* T) {
+  memset(T, 0, sizeof(*T));
+  if (alg == MBO_ALG_RODAS4) {
+    T->nst = 6; T->nexp = 5; T->order = 4; T->gamma = R4_GAMMA;
+    for (int i = 0; i < 5; i++) for (int j = 0; j < 4; j++) T->A[i][j] = R4_A[i][j];
+    for (int i = 0; i < 6; i++) { for (int j = 0; j < 5; j++) T->C[i][j] = R4_C[i][j]; T->CT[i] = R4_CT[i]; T->D[i] = R4_D[i]; }
+    for (int r = 0; r < 2; r++) for (int j = 0; j < 6; j++) T->H[r][j] = R4_H[r][j];
+  } else {
+    T->nst = 8; T->nexp = 6; T->order = 5; T->gamma = RD_GAMMA;
+    for (int i = 0; i < 6; i++) for (int j = 0; j < 5; j++) T->A[i][j] = RD_A[i][j];
+    for (int i = 0; i < 8; i++) { for (int j = 0; j < 7; j++) T->C[i][j] = RD_C[i][j]; T->CT[i] = RD_CT[i]; T->D[i] = RD_D[i]; }
+    for (int r = 0; r < 3; r++) for (int j = 0; j < 8; j++) T->H[r][j] = RD_H[r][j];
+  }
+}
+
 typedef struct {
   const mbo_model* md;
   const double* p;
@@ -50,7 +72,7 @@ static double rms_scaled(int n, const double* e, const double* ua, const double*
 
 /* OrdinaryDiffEq `ode_determine_initdt` (Hairer-Norsett-Wanner II.4), order-5 methods.
  * Algebraic rows (mass 0) carry no derivative information and are left out of d1/d2. */
-static double initial_dt(ctx_t* c, const double* u0, double t0, double t1, const mbo_opts* o, double* w1, double* w2, double* w3) {
+static double initial_dt(ctx_t* c, const double* u0, double t0, double t1, const mbo_opts* o, int order, double* w1, double* w2, double* w3) {
   int n = c->n;
   const int* mass = c->md->mass;
   double dtmax = (o->dtmax > 0) ? o->dtmax : (t1 - t0);
@@ -74,7 +96,7 @@ static double initial_dt(ctx_t* c, const double* u0, double t0, double t1, const
   }
   d2 = sqrt(d2 / n) / dt0;
   double dm = fmax(d1, d2);
-  double dt1 = (dm <= 1e-15) ? fmax(1e-6, dt0 * 1e-3) : pow(10.0, -(2.0 + log10(dm)) / 5.0);
+  double dt1 = (dm <= 1e-15) ? fmax(1e-6, dt0 * 1e-3) : pow(10.0, -(2.0 + log10(dm)) / (double)order);
   return fmin(fmin(100.0 * dt0, dt1), dtmax);
 }
 
@@ -145,8 +167,11 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
                   double* out_tfinal, int32_t* stats /* [5] */) {
   const int n = md->n;
   ctx_t c = {md, p, tb, n, 0, 0, 0, 0, 0};
-  const int rosen = (o->alg == MBO_ALG_RODAS5P);
-  const int nk = rosen ? 8 : 7;
+  const int rosen = (o->alg == MBO_ALG_RODAS5P || o->alg == MBO_ALG_RODAS4);
+  rosen_tab T;
+  rosen_get(o->alg, &T);
+  const int order = rosen ? T.order : 5;
+  const int nk = rosen ? T.nst : 7;
   size_t nd = (size_t)n * (nk + 12) + (size_t)n * n * 2 + md->nnz + 16;
   double* mem = (double*)calloc(nd, sizeof(double));
   int* piv = (int*)calloc(n, sizeof(int));
@@ -171,8 +196,8 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
   while (is < nsave && saveat[is] <= t0) { if (saveat[is] == t0) memcpy(out_u + (size_t)is * n, u, sizeof(double) * n); is++; }
   double t = t0;
   double dtmax = (o->dtmax > 0) ? o->dtmax : (t1 - t0);
-  double dt = (o->dt0 > 0) ? o->dt0 : initial_dt(&c, u, t0, t1, o, w1, w2, w3);
-  const double beta1 = 7.0 / 50.0, beta2 = 2.0 / 25.0, gam = 0.9, qmin = 0.2, qmax = 10.0;
+  double dt = (o->dt0 > 0) ? o->dt0 : initial_dt(&c, u, t0, t1, o, order, w1, w2, w3);
+  const double beta1 = 7.0 / (10.0 * order), beta2 = 2.0 / (5.0 * order), gam = 0.9, qmin = 0.2, qmax = 10.0;
   double qold = 1e-4;
   int64_t maxiters = o->maxiters > 0 ? o->maxiters : 100000;
   int64_t iter = 0;
@@ -209,32 +234,32 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
       f_eval(&c, u, t, du);
       jac_dense(&c, u, t, du, o->jac_mode, J, w1, w2, Jnz);
       dT_eval(&c, u, t, du, o->jac_mode, dT, w2);
-      double cg = 1.0 / (dt * RD_GAMMA);
+      double cg = 1.0 / (dt * T.gamma);
       for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) W[i * n + j] = -J[i * n + j] + ((i == j && mass[i]) ? cg : 0.0);
       if (lu_factor(n, W, piv) != 0) { rc = RC_UNSTABLE; break; }
       memcpy(us, u, sizeof(double) * n);
-      for (int s = 0; s < 8; s++) {
+      for (int s = 0; s < T.nst; s++) {
         if (s > 0) {
-          if (s < 6) {
+          if (s < T.nexp) {
             for (int i = 0; i < n; i++) {
               double a = 0.0;
-              for (int j = 0; j < s; j++) a += RD_A[s][j] * k[(size_t)j * n + i];
+              for (int j = 0; j < s; j++) a += T.A[s][j] * k[(size_t)j * n + i];
               us[i] = u[i] + a;
             }
           } else {
             for (int i = 0; i < n; i++) us[i] += k[(size_t)(s - 1) * n + i];
           }
-          f_eval(&c, us, t + RD_CT[s] * dt, du);
+          f_eval(&c, us, t + T.CT[s] * dt, du);
         }
         for (int i = 0; i < n; i++) {
           double a = 0.0;
-          if (mass[i]) { for (int j = 0; j < s; j++) a += RD_C[s][j] * k[(size_t)j * n + i]; a /= dt; }
-          rhs[i] = du[i] + dt * RD_D[s] * dT[i] + a;
+          if (mass[i]) { for (int j = 0; j < s; j++) a += T.C[s][j] * k[(size_t)j * n + i]; a /= dt; }
+          rhs[i] = du[i] + dt * T.D[s] * dT[i] + a;
         }
         lu_solve_dense(n, W, piv, rhs); c.nsolve++;
         memcpy(k + (size_t)s * n, rhs, sizeof(double) * n);
       }
-      for (int i = 0; i < n; i++) { un[i] = us[i] + k[(size_t)7 * n + i]; err[i] = k[(size_t)7 * n + i]; }
+      for (int i = 0; i < n; i++) { un[i] = us[i] + k[(size_t)(T.nst - 1) * n + i]; err[i] = k[(size_t)(T.nst - 1) * n + i]; }
     }
     EEst = rms_scaled(n, err, u, un, o->abstol, o->reltol);
     if (!isfinite(EEst)) { rc = RC_DTNAN; break; }
@@ -267,7 +292,7 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
           } else {
             for (int i = 0; i < n; i++) {
               double K1 = 0, K2 = 0, K3 = 0;
-              for (int j = 0; j < 8; j++) { double kj = k[(size_t)j * n + i]; K1 += RD_H[0][j] * kj; K2 += RD_H[1][j] * kj; K3 += RD_H[2][j] * kj; }
+              for (int j = 0; j < T.nst; j++) { double kj = k[(size_t)j * n + i]; K1 += T.H[0][j] * kj; K2 += T.H[1][j] * kj; K3 += T.H[2][j] * kj; }
               o_u[i] = (1.0 - th) * u[i] + th * (un[i] + (1.0 - th) * (K1 + th * (K2 + th * K3)));
             }
           }

@@ -16,7 +16,7 @@ def _run_gpu(spec, **kw):
     sys_ = api.multibody(spec.model)
     prob = api.ODEProblem(sys_, tspan=spec.tspan)
     eprob = api.EnsembleProblem(prob, u0_matrix=spec.u0, p_matrix=spec.p)
-    alg = api.Tsit5() if spec.alg == "tsit5" else api.Rodas5P()
+    alg = {"tsit5": api.Tsit5(), "rodas5p": api.Rodas5P(), "rodas4": api.Rodas4()}[spec.alg]
     return api.solve(eprob, alg, api.EnsembleB200(), trajectories=spec.u0.shape[1], saveat=spec.saveat,
                      abstol=spec.abstol, reltol=spec.reltol, **kw)
 
@@ -140,3 +140,11 @@ def test_observed_variables_match_the_oracle_and_the_reference_assertion(oracle)
         np.testing.assert_allclose(got, want, rtol=1e-12, atol=1e-13)
     with pytest.raises(KeyError):
         sol.observed("no.such.variable")
+
+
+@pytest.mark.parametrize("config,N", [("C1", 256), ("C3", 256), ("C4", 128), ("C5", 64)])
+def test_rodas4_parity(oracle, config, N):
+    """Rodas4 (the solver of most reference tests) through both kernel families."""
+    spec = ensembles.make_ensemble(config, N)
+    spec.alg = "rodas4"
+    _compare(_run_gpu(spec), _run_oracle(oracle, spec))

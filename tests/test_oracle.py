@@ -32,7 +32,7 @@ def _scaled_err(u, gold):
     return (np.abs(u - g) / scale).max()
 
 
-@pytest.mark.parametrize("alg", ["tsit5", "rodas5p"])
+@pytest.mark.parametrize("alg", ["tsit5", "rodas5p", "rodas4"])
 def test_pendulum_against_dop853_golden(oracle, alg):
     gold = np.load(os.path.join(GOLD, "pendulum_dop853.npz"))
     spec = ensembles.make_ensemble("C1", 1024)
@@ -44,7 +44,7 @@ def test_pendulum_against_dop853_golden(oracle, alg):
     r = _solve(oracle, spec, gold["index"], alg=alg, abstol=1e-12, reltol=1e-12)
     e12 = _scaled_err(r["u"], gold["u"])
     print(alg, "global error vs DOP853 golden: tol 1e-8 ->", e8, " tol 1e-12 ->", e12)
-    assert e8 < 2e-4 and e12 < 1e-7
+    assert e8 < (2e-4 if alg != "rodas4" else 2e-3) and e12 < (1e-7 if alg != "rodas4" else 1e-6)
 
 
 def test_spring_damper_against_closed_form_golden(oracle):
@@ -123,7 +123,7 @@ def test_robot_forward_difference_jacobian_mode_agrees(oracle):
     assert (np.abs(a["u"] - b["u"]) / scale).max() < 1e-6
 
 
-@pytest.mark.parametrize("alg,order", [("tsit5", 5), ("rodas5p", 5)])
+@pytest.mark.parametrize("alg,order", [("tsit5", 5), ("rodas5p", 5), ("rodas4", 4)])
 def test_fixed_step_convergence_order(oracle, alg, order):
     spec = ensembles.make_ensemble("C1", 1024)
     gold = np.load(os.path.join(GOLD, "pendulum_dop853.npz"))
@@ -235,3 +235,18 @@ def test_observed_expressions(oracle):
     o = oracle.eval_fn("pendulum", 3, np.array([0.3, 1.0]), pen.p0, 0.0, pen.tables.pack())
     x, y = o[pen.observed_names.index("body.r_0[1]")], o[pen.observed_names.index("body.r_0[2]")]
     np.testing.assert_allclose([x, y], [0.5 * np.cos(0.3), 0.5 * np.sin(0.3)], atol=1e-14)
+
+
+def test_rodas4_on_the_dae_and_the_robot(oracle):
+    """Rodas4 is what most reference tests call (test/basic_tests.jl; ropes: Rodas4(autodiff=false));
+    the tableau is restated from memory of the published method, so it is pinned like the others:
+    observed order 4 (above), DOP853 / Radau / Lagrange goldens here."""
+    gf = np.load(os.path.join(GOLD, "fourbar_lagrange.npz"))
+    sf = get_model("fourbar")
+    r = oracle.solve("fourbar", "rodas4", sf.u0[:, None], np.zeros((1, 1)), sf.tables.pack(), (0.0, 1.4399), gf["saveat"],
+                     abstol=1e-9, reltol=1e-9)
+    assert r["retcode"][0] == 1 and np.abs(r["u"][:, :, 0] - gf["u"][0]).max() < 2e-4
+    gr = np.load(os.path.join(GOLD, "robot6dof_radau.npz"))
+    spec = ensembles.make_ensemble("C4", 1)
+    r = _solve(oracle, spec, alg="rodas4")
+    assert r["retcode"][0] == 1 and _scaled_err(r["u"], gr["u"][0:1]) < 1e-6
