@@ -147,6 +147,35 @@ __device__ __noinline__ double initial_dt(const double (&u)[M::N], const double*
   return fmin(fmin(100.0 * dt0, dt1), dtmax);
 }
 
+// Consistent initialisation of the algebraic states of a mass-matrix DAE, per trajectory
+// (the step before the path: MTK's initialisation problem / BrownFullBasicInit in the
+// reference's stack, test/test_fourbar.jl:44,70).  Differential states are kept; 0 = f_alg(u)
+// is solved by Newton for the algebraic states.  A Newton step reuses the generated
+// factor/solve pair with c = 1e20, which pins the differential rows of W = c M - J.
+template <class M>
+__device__ __noinline__ int dae_init(double* u, const double* p, const double* tb, double t0, double abstol,
+                                     double* LU) {
+  constexpr int N = M::N;
+  const double tol = fmin(abstol, 1e-10);
+  int nf = 0;
+  for (int it = 0; it < 10; it++) {
+    double f[N];
+    M::rhs(u, p, t0, tb, f);
+    nf++;
+    double r = 0.0;
+#pragma unroll
+    for (int i = 0; i < N; i++) if (!M::isdiff(i)) r = fmax(r, fabs(f[i]));
+    if (!(r > tol)) break;
+    M::factor(u, p, t0, tb, 1e20, LU);
+#pragma unroll
+    for (int i = 0; i < N; i++) if (M::isdiff(i)) f[i] = 0.0;
+    M::solve(LU, 1e20, p, f);
+#pragma unroll
+    for (int i = 0; i < N; i++) if (!M::isdiff(i)) u[i] += f[i];
+  }
+  return nf;
+}
+
 }  // namespace mbk
 
 namespace mbk {
@@ -191,6 +220,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
         for (int i = 0; i < M::NP; i++) p[i] = a.p[(size_t)i * a.N + traj];
         t = a.t0; is = 0; iter = 0; qold = QOLDINIT;
         naccept = nreject = nf = njac = nsolve = 0;
+        if (ROSEN && !M::IS_ODE) nf += dae_init<M>(u, p, tb, a.t0, a.abstol, LU);
         while (is < a.n_save && a.saveat[is] <= t) {
           if (a.saveat[is] == t) {
 #pragma unroll

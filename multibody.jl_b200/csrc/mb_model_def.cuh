@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
   struct MbModel_##X {                                                                              \
     static constexpr int N = MBM_##X##_N, NP = MBM_##X##_M, NLU = MBM_##X##_NLU,                    \
-                         HAS_DT = MBM_##X##_HAS_DT;                                                 \
+                         HAS_DT = MBM_##X##_HAS_DT, IS_ODE = MBM_##X##_IS_ODE;                      \
     static __device__ __forceinline__ void rhs(const double* u, const double* p, double t,         \
                                                const double* tb, double* du) {                      \
       mbm_##X##_rhs(u, p, t, tb, du);                                                               \

@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         for (int i = 0; i < M::NP; i++) p[i] = a.p[(size_t)i * a.N + traj];
         t = a.t0; is = 0; iter = 0; qold = QOLDINIT;
         naccept = nreject = nf = njac = nsolve = 0;
+        if (!M::IS_ODE) nf += dae_init<M>(u, p, tb, a.t0, a.abstol, LU);
         while (is < a.n_save && a.saveat[is] <= t) {
           if (a.saveat[is] == t) {
 #pragma unroll

@@ -193,9 +193,34 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
 
   memcpy(u, u0, sizeof(double) * n);
   int is = 0;
-  while (is < nsave && saveat[is] <= t0) { if (saveat[is] == t0) memcpy(out_u + (size_t)is * n, u, sizeof(double) * n); is++; }
   double t = t0;
   double dtmax = (o->dtmax > 0) ? o->dtmax : (t1 - t0);
+  /* Consistent initialisation of the algebraic states of a mass-matrix DAE (what MTK's
+   * initialisation problem / OrdinaryDiffEq's BrownFullBasicInit do before the first step,
+   * test/test_fourbar.jl:44,70): differential states are kept, the algebraic equations
+   * 0 = f_alg(u) are solved by Newton for the algebraic states.  One Newton step is a solve
+   * with W = c M - J at c = 1e20, which pins the differential rows. */
+  {
+    int is_dae = 0;
+    for (int i = 0; i < n; i++) if (!mass[i]) is_dae = 1;
+    if (is_dae && rosen) {
+      const double tol_init = fmin(o->abstol, 1e-10);
+      for (int it = 0; it < 10; it++) {
+        f_eval(&c, u, t0, du);
+        double r = 0.0;
+        for (int i = 0; i < n; i++) if (!mass[i]) r = fmax(r, fabs(du[i]));
+        if (!(r > tol_init)) break;
+        jac_dense(&c, u, t0, du, 0, J, w1, w2, Jnz);
+        c.njac--;
+        for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) W[i * n + j] = -J[i * n + j] + ((i == j && mass[i]) ? 1e20 : 0.0);
+        if (lu_factor(n, W, piv) != 0) break;
+        for (int i = 0; i < n; i++) rhs[i] = mass[i] ? 0.0 : du[i];
+        lu_solve_dense(n, W, piv, rhs);
+        for (int i = 0; i < n; i++) if (!mass[i]) u[i] += rhs[i];
+      }
+    }
+  }
+  while (is < nsave && saveat[is] <= t0) { if (saveat[is] == t0) memcpy(out_u + (size_t)is * n, u, sizeof(double) * n); is++; }
   double dt = (o->dt0 > 0) ? o->dt0 : initial_dt(&c, u, t0, t1, o, order, w1, w2, w3);
   const double beta1 = 7.0 / (10.0 * order), beta2 = 2.0 / (5.0 * order), gam = 0.9, qmin = 0.2, qmax = 10.0;
   double qold = 1e-4;

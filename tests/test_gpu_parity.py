@@ -148,3 +148,12 @@ def test_rodas4_parity(oracle, config, N):
     spec = ensembles.make_ensemble(config, N)
     spec.alg = "rodas4"
     _compare(_run_gpu(spec), _run_oracle(oracle, spec))
+
+
+def test_dae_initialisation_on_device_matches_oracle(oracle):
+    spec = ensembles.make_ensemble("C3", 512)
+    spec.u0[0] = ensembles.uniform(np.arange(512), 7, -0.4, 0.4)        # per-trajectory crank angle
+    spec.saveat = np.concatenate([[0.0], spec.saveat])                  # also save the initialised state
+    sol, ref = _run_gpu(spec), _run_oracle(oracle, spec)
+    _compare(sol, ref)
+    assert np.abs(sol.u[0, 2:, :] - ref["u"][0, 2:, :]).max() < 1e-9
