@@ -21,7 +21,7 @@ class Opts(C.Structure):
 def build(force=False):
     if force and os.path.exists(LIB):
         os.remove(LIB)
-    subprocess.check_call(["make", "-C", HERE], stdout=subprocess.DEVNULL)   # no-op when up to date
+    subprocess.check_call(["make", "-C", HERE, "-j8"], stdout=subprocess.DEVNULL)   # no-op when up to date
     return LIB
 
 
