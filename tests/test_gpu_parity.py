@@ -9,6 +9,7 @@ from multibody_jl_b200 import api, ensembles
 from multibody_jl_b200.mechanics.zoo import get_model
 
 pytestmark = pytest.mark.gpu
+ROOT_DIR = __import__("os").path.dirname(__import__("os").path.dirname(__import__("os").path.abspath(__file__)))
 RTOL = 1e-6   # stated tolerance of the north star
 
 
@@ -157,3 +158,46 @@ def test_dae_initialisation_on_device_matches_oracle(oracle):
     sol, ref = _run_gpu(spec), _run_oracle(oracle, spec)
     _compare(sol, ref)
     assert np.abs(sol.u[0, 2:, :] - ref["u"][0, 2:, :]).max() < 1e-9
+
+
+def test_no_saveat_and_solver_options(oracle):
+    """n_save = 0 (only final time / retcode / stats come back) and the dt / dtmax keywords."""
+    spec = ensembles.make_ensemble("C2", 100)
+    sys_ = api.multibody(spec.model)
+    eprob = api.EnsembleProblem(api.ODEProblem(sys_, tspan=spec.tspan), u0_matrix=spec.u0, p_matrix=spec.p)
+    sol = api.solve(eprob, api.Tsit5(), api.EnsembleB200(), trajectories=100, saveat=np.array([]), abstol=1e-8, reltol=1e-8)
+    assert sol.u.shape == (0, 14, 100) and np.all(sol.retcode == 1) and np.all(sol.t_final == spec.tspan[1])
+    a = api.solve(eprob, api.Tsit5(), api.EnsembleB200(), trajectories=100, saveat=spec.saveat, abstol=1e-8, reltol=1e-8,
+                  dt=1e-3, dtmax=0.01)
+    ref = oracle.solve(spec.model, "tsit5", spec.u0, spec.p, sys_.tables.pack(), spec.tspan, spec.saveat, abstol=1e-8,
+                       reltol=1e-8, dt0=1e-3, dtmax=0.01)
+    assert np.abs(a.u - ref["u"]).max() < 1e-9
+    assert a.stats[0].min() >= 500                       # dtmax = 0.01 over 5 s
+
+
+def test_in_process_sharding_over_two_devices(oracle):
+    """mbb200_init(2): one process, contiguous shards on two GPUs (runs only on a multi-GPU box)."""
+    import ctypes as C
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    code = (
+        "import sys; sys.path.insert(0, %r); import mbpkg; mbpkg.load()\n"
+        "import numpy as np\n"
+        "from multibody_jl_b200 import api, ensembles\n"
+        "spec = ensembles.make_ensemble('C2', 1001)\n"
+        "sys_ = api.multibody(spec.model)\n"
+        "ep = api.EnsembleProblem(api.ODEProblem(sys_, tspan=spec.tspan), u0_matrix=spec.u0, p_matrix=spec.p)\n"
+        "kw = dict(trajectories=1001, saveat=spec.saveat[:7], abstol=1e-8, reltol=1e-8, reduction=True)\n"
+        "two = api.solve(ep, api.Tsit5(), api.EnsembleB200(n_gpus=2), **kw)\n"
+        "np.save(sys.argv[1], two.u); np.save(sys.argv[2], two.reduction['raw'])\n" % ROOT_DIR)
+    import tempfile
+    d = tempfile.mkdtemp()
+    subprocess.check_call([sys.executable, "-c", code, d + "/u.npy", d + "/r.npy"])
+    spec = ensembles.make_ensemble("C2", 1001)
+    spec.saveat = spec.saveat[:7]
+    one = _run_gpu(spec, reduction=True)
+    np.testing.assert_array_equal(np.load(d + "/u.npy"), one.u)          # same kernels, same inputs: bit-identical
+    np.testing.assert_allclose(np.load(d + "/r.npy"), one.reduction["raw"], rtol=1e-12)
