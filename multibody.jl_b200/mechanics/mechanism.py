@@ -28,8 +28,14 @@ class Frame:
     """Kinematic state of a frame: r_0, v_0, a_0 in world coordinates, R
     (world->local), w and z = dw/dt resolved locally; plus the wrench sink."""
 
-    def __init__(self, r0, R, w, v0, a0, z):
+    def __init__(self, r0, R, w, v0, a0, z, vl=None, al=None):
         self.r0, self.R, self.w, self.v0, self.a0, self.z = r0, R, w, v0, a0, z
+        # the same origin velocity / (acceleration - gravity) resolved in the frame itself:
+        # vl = R v0, al = R (a0 - g).  Bodies use these, so a serial chain never needs the
+        # absolute rotation matrix (local-frame recursive Newton-Euler); the world-frame
+        # fields above are only emitted when something references them (line forces,
+        # loop closure, observed positions).
+        self.vl, self.al = vl, al
         self.f = [0.0, 0.0, 0.0]     # force the downstream side needs at this frame (local)
         self.tau = [0.0, 0.0, 0.0]
 
@@ -52,12 +58,13 @@ class Mechanism:
     def world(self) -> Frame:
         """World / Fixed at the origin: r_b = 0, R_b = I (components.jl:76-79)."""
         z3 = [0.0, 0.0, 0.0]
-        return Frame(list(z3), eye(), list(z3), list(z3), list(z3), list(z3))
+        return Frame(list(z3), eye(), list(z3), list(z3), list(z3), list(z3), list(z3), vneg(self.gvec))
 
     def fixed(self, r) -> Frame:
         """Fixed(r): components.jl:112-113."""
         z3 = [0.0, 0.0, 0.0]
-        return Frame([float(x) for x in r], eye(), list(z3), list(z3), list(z3), list(z3))
+        return Frame([float(x) for x in r], eye(), list(z3), list(z3), list(z3), list(z3), list(z3),
+                     vneg(self.gvec))
 
     # -- rigid connections ----------------------------------------------------
     def fixed_translation(self, a: Frame, r) -> Frame:
@@ -65,10 +72,11 @@ class Mechanism:
         f_a = f_b, tau_a = tau_b + r x f_b (wrench needed downstream)."""
         r = list(r)
         wr = cross(a.w, r)
+        rel_a = vadd(cross(a.z, r), cross(a.w, wr))
         b = Frame(vadd(a.r0, matTvec(a.R, r)), a.R, a.w,
                   vadd(a.v0, matTvec(a.R, wr)),
-                  vadd(a.a0, matTvec(a.R, vadd(cross(a.z, r), cross(a.w, wr)))),
-                  a.z)
+                  vadd(a.a0, matTvec(a.R, rel_a)),
+                  a.z, vadd(a.vl, wr), vadd(a.al, rel_a))
 
         def back():
             a.add_wrench(b.f, vadd(b.tau, cross(r, b.f)))
@@ -87,7 +95,7 @@ class Mechanism:
         Rw = matvec(Rrel, a.w)
         wb = vadd(Rw, wrel)
         zb = vadd(vsub(matvec(Rrel, a.z), cross(wrel, Rw)), vscale(acc, n))
-        b = Frame(a.r0, matmul(Rrel, a.R), wb, a.v0, a.a0, zb)
+        b = Frame(a.r0, matmul(Rrel, a.R), wb, a.v0, a.a0, zb, matvec(Rrel, a.vl), matvec(Rrel, a.al))
 
         def back():
             a.add_wrench(matTvec(Rrel, b.f), matTvec(Rrel, b.tau))
@@ -112,7 +120,8 @@ class Mechanism:
         rel_a = vadd(vadd(cross(a.z, ns), cross(a.w, wns)),
                      vadd(vscale(2.0, cross(a.w, nv)), vscale(acc, n)))
         b = Frame(vadd(a.r0, matTvec(a.R, ns)), a.R, a.w,
-                  vadd(a.v0, matTvec(a.R, rel_v)), vadd(a.a0, matTvec(a.R, rel_a)), a.z)
+                  vadd(a.v0, matTvec(a.R, rel_v)), vadd(a.a0, matTvec(a.R, rel_a)), a.z,
+                  vadd(a.vl, rel_v), vadd(a.al, rel_a))
 
         def back():
             a.add_wrench(b.f, vadd(b.tau, cross(ns, b.f)))
@@ -154,7 +163,7 @@ class Mechanism:
         Rw = matvec(Rrel, a.w)
         wb = vadd(Rw, wrel)
         zb = vadd(vsub(matvec(Rrel, a.z), cross(wrel, Rw)), wrel_dot)
-        b = Frame(a.r0, matmul(Rrel, a.R), wb, a.v0, a.a0, zb)
+        b = Frame(a.r0, matmul(Rrel, a.R), wb, a.v0, a.a0, zb, matvec(Rrel, a.vl), matvec(Rrel, a.al))
 
         def back():
             a.add_wrench(matTvec(Rrel, b.f), matTvec(Rrel, b.tau))
@@ -176,7 +185,8 @@ class Mechanism:
         wf = self.world()
         accs, Rrel, wrel, wrel_dot, P = self._euler_rotation(wf, seq, phi, phid)
         acc_t = [mb.accel() for _ in range(3)]
-        b = Frame(list(r0), Rrel, wrel, list(v0), list(acc_t), wrel_dot)
+        b = Frame(list(r0), Rrel, wrel, list(v0), list(acc_t), wrel_dot,
+                  matvec(Rrel, list(v0)), matvec(Rrel, vsub(list(acc_t), self.gvec)))
         for i in range(3):
             self._eqs.append((accs[i], phid[i], (lambda i=i: dot(P[i], b.tau)), {}))
             mb.set_rhs(phi[i], phid[i])
@@ -196,15 +206,15 @@ class Mechanism:
         Im = [[I11, I21, I31], [I21, I22, I32], [I31, I32, I33]]
 
         def apply():
-            acc = vsub(fr.a0, self.gvec)
-            v2 = dot(fr.v0, fr.v0)
+            # R (a_0 - g_0 + c |v_0| v_0) = al + c |vl| vl  (rotations preserve the norm)
+            acc = fr.al
+            v2 = dot(fr.vl, fr.vl)
             if not _is_zero(air_resistance) and isinstance(v2, Ex):
                 # |v| v; the 1e-300 keeps d|v|/dv = v/|v| finite (= 0) at rest, where the
                 # reference's finite-difference Jacobian (autodiff=false) sees 0 as well
                 nv = sqrt(v2 + 1e-300)
-                acc = vadd(acc, vscale(air_resistance * nv, fr.v0))
-            lin = vadd(matvec(fr.R, acc),
-                       vadd(cross(fr.z, r_cm), cross(fr.w, cross(fr.w, r_cm))))
+                acc = vadd(acc, vscale(air_resistance * nv, fr.vl))
+            lin = vadd(acc, vadd(cross(fr.z, r_cm), cross(fr.w, cross(fr.w, r_cm))))
             f = vscale(m, lin)
             tau = vadd(vadd(matvec(Im, fr.z), cross(fr.w, matvec(Im, fr.w))), cross(r_cm, f))
             fr.add_wrench(f, tau)
