@@ -55,6 +55,9 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C2":    # spring-damper, 1M parameter sets, Tsit5, 100 saves (spring_damper_system.md:21-63)
         total, model, alg, tol = 1 << 20, "spring_damper", "tsit5", 1e-8
         saveat = 0.05 * np.arange(1, 101)
+    elif config == "C2B":   # three-springs (massless node -> DAE), 1M parameter sets, Rodas5P (three_springs.md:22-44)
+        total, model, alg, tol = 1 << 20, "three_springs", "rodas5p", 1e-8
+        saveat = 0.1 * np.arange(1, 101)
     elif config == "C3":    # fourbar closed loop, 256k crank speeds, Rodas5P (test/test_fourbar.jl:13-46)
         total, model, alg, tol = 1 << 18, "fourbar", "rodas5p", 1e-8
         saveat = np.linspace(0.0, 1.4399, 21)[1:]
@@ -82,6 +85,11 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
         P[sys.param_index("damper1.d")] = d
         P[sys.param_index("body1.m")] = m
         P[sys.param_index("body2.m")] = m
+    elif config == "C2B":
+        P[sys.param_index("spring1.c")] = uniform(idx, 0, 10.0, 40.0)
+        P[sys.param_index("spring3.c")] = uniform(idx, 1, 10.0, 40.0)
+        P[sys.param_index("spring2.c")] = uniform(idx, 2, 20.0, 80.0)
+        P[sys.param_index("body1.m")] = uniform(idx, 3, 0.5, 2.0)
     elif config == "C3":
         U[sys.state_index("j1.w")] = uniform(idx, 0, 3.0, 7.0)
     elif config == "C5":

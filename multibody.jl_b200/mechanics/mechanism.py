@@ -21,7 +21,7 @@ from ..codegen.dag import Ex, sqrt, fmax
 from ..codegen.emit import ldl_solve_factory
 from .builder import ModelBuilder
 from .orientation import (vadd, vsub, vscale, vneg, dot, cross, matvec, matTvec,
-                          matmul, eye, planar_rotation, axes_rotations)
+                          matmul, eye, planar_rotation, axes_rotations, from_Q)
 
 
 class Frame:
@@ -52,6 +52,7 @@ class Mechanism:
         self._back: List[Callable[[], None]] = []   # executed in reverse order
         self._eqs: List[tuple] = []                 # (accel Ex, velocity-state Ex, residual thunk)
         self._bodies: List[Callable[[], None]] = []
+        self._junctions: List[tuple] = []           # (frame, [3 algebraic position states])
         self.frames: Dict[str, Frame] = {}
 
     # -- roots ---------------------------------------------------------------
@@ -195,6 +196,43 @@ class Mechanism:
             mb.set_rhs(r0[i], v0[i])
         return b
 
+    def free_body_quat(self, r0: Sequence[Ex], v0: Sequence[Ex], Qh: Sequence[Ex], w: Sequence[Ex],
+                       k: float = 0.1) -> Frame:
+        """Root `Body(isroot=true, quat=true)` (components.jl:412-418) with the non-unit
+        quaternion of orientation.jl:438-472: states r_0, v_0, Qhat[4], w_a[3];
+        D(Qhat) = Omega(w) Qhat / 2 + k (1 - Qhat'Qhat) Qhat,  Q = Qhat / |Qhat|,  R = from_Q(Q)."""
+        mb = self.mb
+        n = Qh[0] * Qh[0] + Qh[1] * Qh[1] + Qh[2] * Qh[2] + Qh[3] * Qh[3]
+        c = k * (1.0 - n)
+        Om = [[0.0, -w[0], -w[1], -w[2]], [w[0], 0.0, w[2], -w[1]], [w[1], -w[2], 0.0, w[0]], [w[2], w[1], -w[0], 0.0]]
+        for i in range(4):
+            acc = c * Qh[i]
+            for j in range(4):
+                if not (isinstance(Om[i][j], float) and Om[i][j] == 0.0):
+                    acc = acc + 0.5 * (Om[i][j] * Qh[j])
+            mb.set_rhs(Qh[i], acc)
+        rn = 1.0 / sqrt(n)
+        R = from_Q([q * rn for q in Qh])
+        acc_r = [mb.accel() for _ in range(3)]
+        acc_t = [mb.accel() for _ in range(3)]
+        b = Frame(list(r0), R, list(w), list(v0), list(acc_t), list(acc_r),
+                  matvec(R, list(v0)), matvec(R, vsub(list(acc_t), self.gvec)))
+        for i in range(3):
+            self._eqs.append((acc_r[i], w[i], (lambda i=i: b.tau[i]), {}))
+        for i in range(3):
+            self._eqs.append((acc_t[i], v0[i], (lambda i=i: matTvec(b.R, b.f)[i]), {}))
+            mb.set_rhs(r0[i], v0[i])
+        return b
+
+    def junction(self, r: Sequence[Ex]) -> Frame:
+        """Massless connection point of force elements (the node where spring1, spring2 and
+        spring3 of docs/src/examples/three_springs.md:22-44 meet): its position is an algebraic
+        state fixed by the force balance 0 = sum of the forces acting on it."""
+        z3 = [0.0, 0.0, 0.0]
+        fr = Frame(list(r), eye(), list(z3), list(z3), list(z3), list(z3), list(z3), vneg(self.gvec))
+        self._junctions.append((fr, list(r)))
+        return fr
+
     # -- bodies and forces ------------------------------------------------------
     def body(self, fr: Frame, m, r_cm=(0.0, 0.0, 0.0), I=(0.001, 0.001, 0.001, 0.0, 0.0, 0.0),
              air_resistance=0.0):
@@ -256,6 +294,9 @@ class Mechanism:
             apply()
         for back in reversed(self._back):
             back()
+        for fr, rs in self._junctions:              # algebraic rows: force balance of the node
+            for i in range(3):
+                mb.set_rhs(rs[i], _ex(mb, fr.f[i]))
         accs = [e[0] for e in self._eqs]
         res = [_ex(mb, e[2]()).n for e in self._eqs]
         acc_nodes = [a.n for a in accs]

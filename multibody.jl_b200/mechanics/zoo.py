@@ -70,6 +70,39 @@ def spring_damper() -> ReducedSystem:
     return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
 
 
+def three_springs() -> ReducedSystem:
+    """C2, second model.  docs/src/examples/three_springs.md:22-44 (test/basic_tests.jl:440-481):
+    `body1` is a free root body with the non-unit quaternion (13 states) hanging on `spring2`
+    from the massless node where `spring1` (from bar1 = [0.3,0,0]) and `spring3` (from bar2 =
+    [0,0,0.3]) meet.  The node position is algebraic (force balance) -> index-1 DAE, n = 16,
+    which is why the reference solves it with Rodas5P / Rodas4 and not Tsit5."""
+    mb = ModelBuilder("three_springs")
+    mech = Mechanism(mb)
+    c1 = mb.param("spring1.c", 20.0)
+    c2 = mb.param("spring2.c", 40.0)
+    c3 = mb.param("spring3.c", 20.0)
+    m = mb.param("body1.m", 0.8)
+    s0 = 0.1
+    r0 = [mb.state(f"body1.r_0[{i+1}]", v) for i, v in enumerate((0.5, -0.3, 0.0))]
+    v0 = [mb.state(f"body1.v_0[{i+1}]", 0.0) for i in range(3)]
+    Qh = [mb.state(f"body1.Q\u0302[{i+1}]", v) for i, v in enumerate((1.0, 0.0, 0.0, 0.0))]
+    w = [mb.state(f"body1.w_a[{i+1}]", 0.0) for i in range(3)]
+    rj = [mb.state(f"spring1.frame_b.r_0[{i+1}]", v, differential=False) for i, v in enumerate((0.1, -0.2, 0.2))]
+    world = mech.world()
+    bar1 = mech.fixed_translation(world, (0.3, 0.0, 0.0))
+    bar2 = mech.fixed_translation(world, (0.0, 0.0, 0.3))
+    b1 = mech.free_body_quat(r0, v0, Qh, w)
+    mech.body(b1, m, (0.0, -0.2, 0.0), (0.1, 0.1, 0.1, 0.0, 0.0, 0.0))
+    node = mech.junction(rj)
+    mech.line_force(bar1, node, lambda sl, ds: c1 * (sl - s0))       # spring1
+    mech.line_force(bar2, node, lambda sl, ds: c3 * (sl - s0))       # spring3
+    mech.line_force(node, b1, lambda sl, ds: c2 * (sl - s0))         # spring2
+    mech.solve_accelerations()
+    for c in range(3):
+        mb.observed[f"body1.r_0[{c+1}]"] = r0[c].n
+    return mb.finish(tspan=(0.0, 10.0), mechanism=mech)
+
+
 def consistent_positions(sysm_g, closure, q_nodes, q0, dep, iters: int = 50, tol: float = 1e-14):
     """Newton on the closure conditions g(q) = 0 for the dependent coordinates (the
     reference leaves this to MTK's initialisation problem, test/test_fourbar.jl:44,70)."""
@@ -186,6 +219,7 @@ MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "spring_damper": spring_damper,
     "robot6dof": robot6dof,
     "fourbar": fourbar,
+    "three_springs": three_springs,
     "rope6": rope,
 }
 _cache: Dict[str, ReducedSystem] = {}

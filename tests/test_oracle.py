@@ -266,3 +266,35 @@ def test_dae_consistent_initialisation_per_trajectory(oracle):
         assert r["u"][0, 0, k] == u0[0, k] and r["u"][0, 1, k] == u0[1, k]          # differential states untouched
         assert np.abs(sysm.eval_rhs(r["u"][0, :, k], sysm.p0, 0.0)[2:]).max() < 1e-10
     np.testing.assert_allclose(r["u"][0, :, 0], sysm.u0, atol=1e-14)                 # already consistent: unchanged
+
+
+def test_three_springs_quaternion_body_and_massless_node(oracle):
+    """C2's second model (docs/src/examples/three_springs.md:22-44; retcode success is what
+    test/basic_tests.jl:481 asserts).  Pins the non-unit quaternion equations
+    (src/orientation.jl:438-472) and the node force balance: total energy evaluated with scipy's
+    quaternion -> rotation is conserved, |Qhat| stays 1, the algebraic rows vanish at t0 after
+    the consistent initialisation."""
+    from scipy.spatial.transform import Rotation
+    s = get_model("three_springs")
+    assert s.n == 16 and list(s.mass_diag) == [1] * 13 + [0] * 3
+    sv = np.linspace(0.0, 10.0, 51)
+    r = oracle.solve("three_springs", "rodas5p", s.u0[:, None], s.p0[:, None], s.tables.pack(), (0.0, 10.0), sv,
+                     abstol=1e-9, reltol=1e-9)
+    assert r["retcode"][0] == 1
+    c1, c2, c3, m = s.p0
+
+    def energy(u):
+        r0, v0, Q, w, rj = u[0:3], u[3:6], u[6:10], u[10:13], u[13:16]
+        q = Q / np.linalg.norm(Q)
+        T = Rotation.from_quat([q[1], q[2], q[3], q[0]]).as_matrix()          # local -> world
+        rcm = np.array([0.0, -0.2, 0.0])
+        vcm = v0 + T @ np.cross(w, rcm)
+        E = 0.5 * m * vcm @ vcm + 0.5 * 0.1 * w @ w + m * 9.80665 * (r0 + T @ rcm)[1]
+        for c, a, b in ((c1, np.array([0.3, 0, 0]), rj), (c3, np.array([0, 0, 0.3]), rj), (c2, rj, r0)):
+            E += 0.5 * c * (np.linalg.norm(b - a) - 0.1) ** 2
+        return E
+    E = np.array([energy(r["u"][k, :, 0]) for k in range(len(sv))])
+    assert np.abs(E - E[0]).max() < 1e-6
+    assert abs(np.linalg.norm(r["u"][-1, 6:10, 0]) - 1.0) < 1e-6
+    assert np.abs(s.eval_rhs(r["u"][0, :, 0], s.p0, 0.0)[13:]).max() < 1e-10
+    assert np.abs(r["u"][:, 0:3, 0]).max() < 2.0                                   # the body stays suspended
