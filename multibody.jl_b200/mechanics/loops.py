@@ -65,10 +65,21 @@ class LoopMechanism(Mechanism):
         self._cuts.append(cut)
         return cut
 
+    def cut_revolute_planar(self, a: Frame, b: Frame, n):
+        """RevolutePlanarLoopConstraint (src/joints.jl:593-651): for mechanisms moving in the plane
+        normal to n only the two in-plane components of frame_a.r_0 ~ frame_b.r_0 are imposed
+        (the joint transmits only the in-plane constraint forces f_c)."""
+        e1, e2 = _perp(n)
+        cut = dict(a=a, b=b, n=[float(x) for x in n], e1=e1, e2=e2, planar=True)
+        self._cuts.append(cut)
+        return cut
+
     @staticmethod
     def closure_residuals(cut) -> List[Ex]:
         a, b = cut["a"], cut["b"]
         r_rel = matvec(a.R, vsub(b.r0, a.r0))                   # frame_a.r_0 ~ frame_b.r_0
+        if cut.get("planar"):
+            return [dot(cut["e1"], r_rel), dot(cut["e2"], r_rel)]
         Rrel = matmul(b.R, transpose(a.R))                      # a-coordinates -> b-coordinates
         nb = matvec(Rrel, cut["n"])                             # the axis must be the same in both
         return [r_rel[0], r_rel[1], r_rel[2], dot(cut["e1"], nb), dot(cut["e2"], nb)]

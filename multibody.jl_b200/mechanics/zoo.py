@@ -214,12 +214,54 @@ def rope(n_links: int = 6, name: str = "rope6") -> ReducedSystem:
     return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
 
 
+def fourbar_planar() -> ReducedSystem:
+    """Planar loop of docs/src/examples/kinematic_loops.md:38-80: four bars of length 1.5, five
+    revolute joints about z (two of them at the world origin), the loop closed by
+    `RevolutePlanarLoopConstraint` j4, dampers (d = 0.1) on j1 and j2.  Two degrees of freedom:
+    j1, j2 keep (phi, w) as differential states; j3 and j5 are algebraic.  j5 is traversed from
+    the world side, so its coordinate here is the reversed angle -j5.phi."""
+    mb = ModelBuilder("fourbar_planar")
+    mech = LoopMechanism(mb)
+    d1 = mb.param("damper1.d", 0.1)
+    d2 = mb.param("damper2.d", 0.1)
+    L = 1.5
+    q1 = mb.state("j1.phi", 0.1)
+    w1 = mb.state("j1.w", 0.0)
+    q2 = mb.state("j2.phi", 0.0)
+    w2 = mb.state("j2.w", 0.0)
+    q3 = mb.state("j3.phi", 0.0, differential=False)
+    q5 = mb.state("j5.phi_rev", 0.0, differential=False)
+    v3, v5 = mech.dependent_velocity(q3), mech.dependent_velocity(q5)
+    world = mech.world()
+    j1 = mech.revolute(world, (0, 0, 1), q1, w1, tau_applied=-d1 * w1, name="j1")
+    b1 = mech.body_shape(j1, (L, 0.0, 0.0), 1.0)
+    j2 = mech.revolute(b1, (0, 0, 1), q2, w2, tau_applied=-d2 * w2, name="j2")
+    b2 = mech.body_shape(j2, (0.0, L, 0.0), 1.0)
+    j3 = mech.revolute(b2, (0, 0, 1), q3, v3, name="j3")
+    b3 = mech.body_shape(j3, (-L, 0.0, 0.0), 1.0)
+    j5 = mech.revolute(world, (0, 0, 1), q5, v5, name="j5")            # frame = j5.frame_a = b4.frame_b
+    b4a = mech.fixed_translation(j5, (0.0, L, 0.0))                     # back along b4 (r = [0,-L,0]) to b4.frame_a
+    mech.body(b4a, 1.0, (0.0, -L / 2, 0.0))
+    mech.cut_revolute_planar(b3, b4a, (0, 0, 1))
+    q_all = [q1, q2, q3, q5]
+    v_all = [w1, w2, v3, v5]
+    mech.solve_loops(q_all, v_all)
+    q0 = consistent_positions(mb.g, mech.closure, [q.n for q in q_all], [mb.u0[mb.index_of(q)] for q in q_all],
+                              mech.dep)
+    for q, v in zip(q_all, q0):
+        mb.u0[mb.index_of(q)] = float(v)
+    sysm = mb.finish(tspan=(0.0, 10.0), mechanism=mech)
+    sysm.meta["pivots"] = static_pivots(sysm)
+    return sysm
+
+
 MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "pendulum": pendulum,
     "spring_damper": spring_damper,
     "robot6dof": robot6dof,
     "fourbar": fourbar,
     "three_springs": three_springs,
+    "fourbar_planar": fourbar_planar,
     "rope6": rope,
 }
 _cache: Dict[str, ReducedSystem] = {}

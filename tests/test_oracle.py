@@ -298,3 +298,41 @@ def test_three_springs_quaternion_body_and_massless_node(oracle):
     assert abs(np.linalg.norm(r["u"][-1, 6:10, 0]) - 1.0) < 1e-6
     assert np.abs(s.eval_rhs(r["u"][0, :, 0], s.p0, 0.0)[13:]).max() < 1e-10
     assert np.abs(r["u"][:, 0:3, 0]).max() < 2.0                                   # the body stays suspended
+
+
+def test_planar_loop_constraint_energy_balance(oracle):
+    """RevolutePlanarLoopConstraint (src/joints.jl:593-651) on the planar four-bar of
+    docs/src/examples/kinematic_loops.md:38-80 (two degrees of freedom, dampers on j1, j2):
+    mechanical energy from an independent planar forward kinematics plus the energy dissipated
+    in the two dampers stays constant, and the loop stays closed."""
+    s = get_model("fourbar_planar")
+    assert list(s.mass_diag) == [1, 1, 1, 1, 0, 0]
+    L, m, I33, g, d = 1.5, 1.0, 0.001, 9.80665, 0.1
+    # up to t = 1.4: at t ~ 1.54 the parallelogram passes next to its flat (singular) configuration
+    sv = np.linspace(0.0, 1.4, 2801)
+    r = oracle.solve("fourbar_planar", "rodas5p", s.u0[:, None], s.p0[:, None], s.tables.pack(), (0.0, 1.4), sv,
+                     abstol=1e-10, reltol=1e-10)
+    assert r["retcode"][0] == 1
+    u = r["u"][:, :, 0]
+    q1, w1, q2, w2, q3, q5 = (u[:, k] for k in range(6))
+    th1, th2, th3, th4 = q1, q1 + q2, q1 + q2 + q3, q5
+    A = L * np.stack([np.cos(th1), np.sin(th1)])
+    B = A + L * np.stack([-np.sin(th2), np.cos(th2)])
+    C = B - L * np.stack([np.cos(th3), np.sin(th3)])
+    F4 = L * np.stack([-np.sin(th4), np.cos(th4)])                 # b4.frame_a seen from the world pivot
+    assert np.abs(C - F4).max() < 1e-7                             # loop closed
+    coms = [0.5 * A, 0.5 * (A + B), 0.5 * (B + C), 0.5 * F4]
+    dt = sv[1] - sv[0]
+    E = np.zeros(len(sv))
+    for c, th in zip(coms, (th1, th2, th3, th4)):
+        v = np.gradient(c, dt, axis=1, edge_order=2)
+        om = np.gradient(th, dt, edge_order=2)
+        E += 0.5 * m * (v ** 2).sum(axis=0) + 0.5 * I33 * om ** 2 + m * g * c[1]
+    P = d * (w1 ** 2 + w2 ** 2)
+    diss = np.concatenate([[0.0], np.cumsum(0.5 * (P[1:] + P[:-1]) * dt)])
+    bal = E + diss
+    assert np.abs(bal[5:-5] - bal[5]).max() < 2e-4 * max(1.0, np.abs(E).max())
+    assert diss[-1] > 0.05                                          # the dampers did take energy out
+    full = oracle.solve("fourbar_planar", "rodas5p", s.u0[:, None], s.p0[:, None], s.tables.pack(), (0.0, 10.0),
+                        np.array([10.0]))
+    assert full["retcode"][0] == 1                                 # the docs run (0, 10) with default tolerances
