@@ -63,7 +63,7 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
         saveat = np.linspace(0.0, 1.4399, 21)[1:]
     elif config == "C3P":   # planar loop with RevolutePlanarLoopConstraint (kinematic_loops.md:38-80), initial crank angles
         total, model, alg, tol = 1 << 16, "fourbar_planar", "rodas5p", 1e-8
-        saveat = np.linspace(0.0, 1.4, 21)[1:]
+        saveat = np.linspace(0.0, 0.6, 21)[1:]
     elif config == "C4":    # Robot6DOF parameter sweep, 1M, Rodas5P reltol 1e-8 (test/test_robot.jl:268-288)
         total, model, alg, tol = 1 << 20, "robot6dof", "rodas5p", 1e-8
         saveat = np.linspace(0.0, 2.0, 21)
@@ -96,7 +96,7 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C3":
         U[sys.state_index("j1.w")] = uniform(idx, 0, 3.0, 7.0)
     elif config == "C3P":
-        U[sys.state_index("j1.phi")] = uniform(idx, 0, 0.05, 0.3)     # dependents are re-initialised on the device
+        U[sys.state_index("j1.phi")] = uniform(idx, 0, 0.05, 0.2)     # dependents are re-initialised on the device
         P[sys.param_index("damper1.d")] = uniform(idx, 1, 0.05, 0.5)
         P[sys.param_index("damper2.d")] = uniform(idx, 2, 0.05, 0.5)
     elif config == "C5":
@@ -109,6 +109,7 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
             P[sys.param_index(f"axis{a+1}.controller.kp")] = uniform(idx, 1 + 3 * a, 3.0, 8.0)
             P[sys.param_index(f"axis{a+1}.controller.ks")] = uniform(idx, 2 + 3 * a, 0.3, 0.8)
             P[sys.param_index(f"axis{a+1}.controller.Ts")] = uniform(idx, 3 + 3 * a, 0.03, 0.08)
-    tspan = (0.0, 1.4) if config == "C3P" else tuple(sys.meta["tspan"])
+    tspan = (0.0, 0.6) if config == "C3P"   # stops short of the flat (singular) configuration of the parallelogram
+    tspan = tspan if config == "C3P" else tuple(sys.meta["tspan"])
     return EnsembleSpec(config, model, alg, tspan, saveat, tol, tol,
                         np.ascontiguousarray(U), np.ascontiguousarray(P), total)
