@@ -109,7 +109,7 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
             P[sys.param_index(f"axis{a+1}.controller.kp")] = uniform(idx, 1 + 3 * a, 3.0, 8.0)
             P[sys.param_index(f"axis{a+1}.controller.ks")] = uniform(idx, 2 + 3 * a, 0.3, 0.8)
             P[sys.param_index(f"axis{a+1}.controller.Ts")] = uniform(idx, 3 + 3 * a, 0.03, 0.08)
-    tspan = (0.0, 0.6) if config == "C3P"   # stops short of the flat (singular) configuration of the parallelogram
-    tspan = tspan if config == "C3P" else tuple(sys.meta["tspan"])
+    # C3P stops short of the flat (singular) configuration of the parallelogram
+    tspan = (0.0, 0.6) if config == "C3P" else tuple(sys.meta["tspan"])
     return EnsembleSpec(config, model, alg, tspan, saveat, tol, tol,
                         np.ascontiguousarray(U), np.ascontiguousarray(P), total)
