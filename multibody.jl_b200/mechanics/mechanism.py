@@ -284,6 +284,21 @@ class Mechanism:
             b.add_wrench(matvec(b.R, fw), [0.0, 0.0, 0.0])
         self._bodies.append(apply)
 
+    def world_force(self, b: Frame, f, resolve_world=1.0):
+        """WorldForce (forces.jl:161-170, 216-226): external force on frame b, `f` given in world
+        coordinates (`resolve_frame=:world`, frame_b.f ~ -resolve2(R_b, f)) or in frame_b itself
+        (`:frame_b`, frame_b.f ~ -f).  `resolve_world` is 1 / 0 or a parameter blending the two,
+        so one compiled kernel set serves both variants."""
+        def apply():
+            fl = list(f)
+            fw = matvec(b.R, fl)
+            if isinstance(resolve_world, (int, float)):
+                F = fw if resolve_world else fl
+            else:
+                F = [resolve_world * fw[i] + (1.0 - resolve_world) * fl[i] for i in range(3)]
+            b.add_wrench(vneg(F), [0.0, 0.0, 0.0])
+        self._bodies.append(apply)
+
     # -- assembly -----------------------------------------------------------------
     def solve_accelerations(self):
         """Close the model: accumulate wrenches leaf->root, form the joint equations

@@ -103,6 +103,64 @@ def three_springs() -> ReducedSystem:
     return mb.finish(tspan=(0.0, 10.0), mechanism=mech)
 
 
+def free_couple() -> ReducedSystem:
+    """test/test_worldforces.jl:96-213 (TestWorldForce3/4/5/7): a free `BodyShape` / `BodyCylinder`
+    (r = [1,0,0], root with Euler angles, no gravity) with `WorldForce` f on frame_a and -f on
+    frame_b, resolved in the world or in frame_b.  The reference prints 16-digit end positions
+    of `body.frame_a.r_0` for these; they are the tightest reference-run outputs the oracle can
+    be checked against (tests/golden/reference_known_answers.json)."""
+    mb = ModelBuilder("free_couple")
+    mech = Mechanism(mb, g=0.0)
+    f = [mb.param(f"f[{i+1}]", v) for i, v in enumerate((0.0, 1.0, 0.0))]
+    rw = mb.param("resolve_world", 1.0)
+    m = mb.param("body.m", 1.0)
+    I = [mb.param(f"body.I_{k}{k}", 0.001) for k in (1, 2, 3)]
+    r0 = [mb.state(f"body.r_0[{i+1}]", 0.0) for i in range(3)]
+    v0 = [mb.state(f"body.v_0[{i+1}]", 0.0) for i in range(3)]
+    phi = [mb.state(f"body.phi[{i+1}]", 0.0) for i in range(3)]
+    phid = [mb.state(f"body.phid[{i+1}]", 0.0) for i in range(3)]
+    a = mech.free_body_euler(r0, v0, phi, phid)
+    b = mech.body_shape(a, (1.0, 0.0, 0.0), m, I=(I[0], I[1], I[2], 0.0, 0.0, 0.0))
+    mech.world_force(a, f, rw)
+    mech.world_force(b, [-x for x in f], rw)
+    mech.solve_accelerations()
+    for c in range(3):
+        mb.observed[f"body.frame_a.r_0[{c+1}]"] = r0[c].n
+    return mb.finish(tspan=(0.0, 1.0), mechanism=mech)
+
+
+def furuta() -> ReducedSystem:
+    """Furuta pendulum of test/test_orientation_getters.jl:3-47 (docs/src/examples/... rotations):
+    shoulder Revolute(n=y) -> upper_arm BodyShape(r=[0,0,0.6]) -> elbow Revolute(n=z, phi0=0.1) ->
+    lower_arm BodyShape(r=[0,0.6,0]) -> tip Body(m=0.3); Rotational.Damper(d=0.07) on both axes;
+    g = 9.81.  The reference prints `get_trans` of two frames from a Rodas5P() solve: the only
+    reference-run output of the Rosenbrock path (tests/golden/reference_known_answers.json)."""
+    mb = ModelBuilder("furuta")
+    mech = Mechanism(mb, g=9.81)
+    d1 = mb.param("damper1.d", 0.07)
+    d2 = mb.param("damper2.d", 0.07)
+    p1 = mb.state("shoulder_joint.phi", 0.0)
+    w1 = mb.state("shoulder_joint.w", 0.0)
+    p2 = mb.state("elbow_joint.phi", 0.1)
+    w2 = mb.state("elbow_joint.w", 0.0)
+    sh = mech.revolute(mech.world(), (0, 1, 0), p1, w1, tau_applied=-d1 * w1, name="shoulder_joint")
+    ua_b = mech.body_shape(sh, (0.0, 0.0, 0.6), 1.0)
+    el = mech.revolute(ua_b, (0, 0, 1), p2, w2, tau_applied=-d2 * w2, name="elbow_joint")
+    la_b = mech.body_shape(el, (0.0, 0.6, 0.0), 1.0)
+    mech.body(la_b, 0.3)
+    for c in range(3):
+        mb.observed[f"upper_arm.frame_b.r_0[{c+1}]"] = _node(mb, ua_b.r0[c])
+    for c in range(3):
+        mb.observed[f"lower_arm.frame_b.r_0[{c+1}]"] = _node(mb, la_b.r0[c])
+    mech.solve_accelerations()
+    return mb.finish(tspan=(0.0, 12.0), mechanism=mech)
+
+
+def _node(mb, v):
+    from .mechanism import _ex
+    return _ex(mb, v).n
+
+
 def consistent_positions(sysm_g, closure, q_nodes, q0, dep, iters: int = 50, tol: float = 1e-14):
     """Newton on the closure conditions g(q) = 0 for the dependent coordinates (the
     reference leaves this to MTK's initialisation problem, test/test_fourbar.jl:44,70)."""
@@ -263,6 +321,8 @@ MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "three_springs": three_springs,
     "fourbar_planar": fourbar_planar,
     "rope6": rope,
+    "free_couple": free_couple,
+    "furuta": furuta,
 }
 _cache: Dict[str, ReducedSystem] = {}
 

@@ -53,7 +53,7 @@ def test_generated_jacobian_and_dT_match_finite_differences(oracle, name):
             e = np.zeros(sysm.n); e[j] = h
             fd = (f(u + e) - f(u - e)) / (2 * h)
             scale = np.maximum(np.abs(J[:, j]), 1.0) * max(1.0, np.abs(J).max() * 1e-6)
-            assert (np.abs(fd - J[:, j]) / scale).max() < (2e-5 if sysm.n < 40 else 5e-4), (name, j)   # FD truncation grows with the rope accelerations
+            assert (np.abs(fd - J[:, j]) / scale).max() < (1e-4 if sysm.n < 40 else 5e-4), (name, j)   # FD truncation: h^2 f''' grows with 1/inertia (free_couple) and the rope accelerations
         dT = oracle.eval_fn(name, 2, u, p, t, tb)
         h = 1e-7
         fd = (f(u, t + h) - f(u, t - h)) / (2 * h)
