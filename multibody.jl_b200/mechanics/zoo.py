@@ -161,6 +161,22 @@ def _node(mb, v):
     return _ex(mb, v).n
 
 
+def planar_pendulum() -> ReducedSystem:
+    """test/test_PlanarMechanics.jl:38-61: `Pl.Fixed -> Pl.Revolute -> Pl.FixedTranslation(r=[1,0]) ->
+    Pl.Body(m=1, I=0.1)`, gy = -9.80665; two states (test asserts `length(unknowns) == 2`).
+    The same mechanism in 3-D: Revolute about z, point mass at [1,0,0] with I_33 = 0.1.  The
+    reference prints `rod.frame_a.phi` at t = 1 from a `Rodas5P()` run at default tolerances."""
+    mb = ModelBuilder("planar_pendulum")
+    mech = Mechanism(mb)
+    phi = mb.state("body.phi", 0.0)
+    w = mb.state("body.w", 0.0)
+    jb = mech.revolute(mech.world(), (0, 0, 1), phi, w, name="revolute")
+    mech.body(jb, 1.0, (1.0, 0.0, 0.0), (0.001, 0.001, 0.1, 0.0, 0.0, 0.0))
+    mech.solve_accelerations()
+    mb.observed["rod.frame_a.phi"] = phi.n
+    return mb.finish(tspan=(0.0, 3.0), mechanism=mech)
+
+
 def consistent_positions(sysm_g, closure, q_nodes, q0, dep, iters: int = 50, tol: float = 1e-14):
     """Newton on the closure conditions g(q) = 0 for the dependent coordinates (the
     reference leaves this to MTK's initialisation problem, test/test_fourbar.jl:44,70)."""
@@ -323,6 +339,7 @@ MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "rope6": rope,
     "free_couple": free_couple,
     "furuta": furuta,
+    "planar_pendulum": planar_pendulum,
 }
 _cache: Dict[str, ReducedSystem] = {}
 

@@ -234,3 +234,10 @@ def test_device_result_equals_reference_run_output():
     assert np.abs(ua - np.array(case["upper_arm_frame_b_t1"])).max() < case["atol_t1"]
     ref12 = np.array(case["lower_arm_frame_b_t12"])
     assert np.linalg.norm(la - ref12) < case["rtol_t12"] * np.linalg.norm(ref12)
+    case = KA["planar_pendulum_rodas5p_default_tolerances"]
+    ps = api.multibody("planar_pendulum")
+    sol = api.solve(api.EnsembleProblem(api.ODEProblem(ps, tspan=(0.0, 3.0))), api.Rodas5P(), api.EnsembleB200(),
+                    trajectories=3, saveat=np.array([1.0, 2.0]), abstol=case["abstol"], reltol=case["reltol"])
+    assert api.successful_retcode(sol)
+    assert np.abs(sol.u[0, 0, :] - case["rod_frame_a_phi_t1"]).max() < 1e-4
+    assert np.abs(sol.u[1, 0, :] - case["rod_frame_a_phi_t2"]).max() < case["atol"]

@@ -409,3 +409,21 @@ def test_reference_run_outputs_rodas5p_furuta(oracle):
         assert np.linalg.norm(out[tag][1] - ref12) < case["rtol_t12"] * np.linalg.norm(ref12)
     assert np.abs(out["tight"][0] - ref1).max() < 1.5e-4          # the reference run's own error at reltol 1e-3
     assert abs(out["tight"][1][1] + 0.6) < 1e-6                    # fully damped: hangs straight down
+
+
+def test_reference_run_output_rodas5p_planar_pendulum(oracle):
+    """test/test_PlanarMechanics.jl:56-60: `Rodas5P()` at default tolerances, phi(1) printed to 16
+    digits and asserted at atol 1e-2.  The oracle lands 3.8e-5 from the printed value and the
+    converged solution 7.9e-5 from it: consistent, but again not step-identical."""
+    case = KA["planar_pendulum_rodas5p_default_tolerances"]
+    sys_ = get_model("planar_pendulum")
+    u0 = np.array(sys_.u0, float)[:, None]
+    p = np.zeros((0, 1))
+    sv = np.array([1.0, 2.0])
+    r = oracle.solve("planar_pendulum", "rodas5p", u0, p, sys_.tables.pack(), (0.0, 3.0), sv,
+                     abstol=case["abstol"], reltol=case["reltol"])
+    assert r["retcode"][0] == 1
+    assert abs(r["u"][0, 0, 0] - case["rod_frame_a_phi_t1"]) < 1e-4
+    assert abs(r["u"][1, 0, 0] - case["rod_frame_a_phi_t2"]) < case["atol"]
+    tight = oracle.solve("planar_pendulum", "rodas5p", u0, p, sys_.tables.pack(), (0.0, 3.0), sv, abstol=1e-13, reltol=1e-13)
+    assert abs(tight["u"][0, 0, 0] - case["rod_frame_a_phi_t1"]) < 1e-4
