@@ -70,6 +70,9 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C5":    # stiff 6-link rope of docs/src/examples/ropes_and_cables.md:24-36, 64k parameter sets
         total, model, alg, tol = 1 << 16, "rope6", "rodas5p", 1e-6
         saveat = np.linspace(0.0, 5.0, 51)[1:]
+    elif config == "C5E":   # flexible rope (c = 800, d = 0.01; ropes_and_cables.md:48-60) at the 3-link size of test/basic_tests.jl:928
+        total, model, alg, tol = 1 << 16, "rope3e", "rodas5p", 1e-6
+        saveat = np.linspace(0.0, 5.0, 51)[1:]
     else:
         raise KeyError(f"config {config} is not built (C1..C5 are; C5 at the documented 6-link size)")
     N = total if N is None else int(N)
@@ -102,6 +105,11 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C5":
         P[sys.param_index("rope.d_joint")] = uniform(idx, 0, 0.5, 2.0)
         P[sys.param_index("body.m")] = uniform(idx, 1, 0.5, 2.0)
+        P[sys.param_index("rope.air_resistance")] = uniform(idx, 2, 0.0, 0.4)
+    elif config == "C5E":
+        P[sys.param_index("rope.d")] = 0.01
+        P[sys.param_index("rope.d_joint")] = uniform(idx, 0, 0.05, 0.2)
+        P[sys.param_index("body.m")] = uniform(idx, 1, 100.0, 500.0)
         P[sys.param_index("rope.air_resistance")] = uniform(idx, 2, 0.0, 0.4)
     elif config == "C4":
         P[sys.param_index("mechanics.load.m")] = uniform(idx, 0, 5.0, 25.0)

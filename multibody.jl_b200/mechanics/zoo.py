@@ -288,6 +288,44 @@ def rope(n_links: int = 6, name: str = "rope6") -> ReducedSystem:
     return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
 
 
+def rope_elastic(n_links: int = 3, name: str = "rope3e") -> ReducedSystem:
+    """Flexible `Rope(l=1, m=5, n=3, c=800, d=0.001, d_joint=0.1, air_resistance=0.2)` with a 300 kg
+    `Body` at its end (test/basic_tests.jl:928-959; docs/src/examples/ropes_and_cables.md:48-60).
+    With c > 0 every link is a `Prismatic(n=dir, s0=l/n)` in parallel with `Translational.Spring(
+    c n, s_rel0 = l/n)` and `Damper(d n)`, its mass a `Body(m/n, r_cm = l/(2n) dir)` on the link's
+    frame_a (src/components.jl:594-611).  States 6 (n+1) + 2 n = 8 n + 6 = 30 for n = 3, the count
+    the reference's test perturbs (basic_tests.jl:950-959)."""
+    mb = ModelBuilder(name)
+    mech = Mechanism(mb)
+    d_joint = mb.param("rope.d_joint", 0.1)
+    m_body = mb.param("body.m", 300.0)
+    air = mb.param("rope.air_resistance", 0.2)
+    c = mb.param("rope.c", 800.0)
+    d = mb.param("rope.d", 0.001)
+    l, m_rope = 1.0, 5.0
+    dirv = np.array([0.0, -1.0, 0.0])
+    li, mi = l / n_links, m_rope / n_links
+    ci, di = n_links * c, n_links * d
+    fr = mech.world()
+    init = {0: (0.4, 0.0, 0.6)}                 # released from a deflected first joint
+    for i in range(n_links + 1):
+        a0 = init.get(i, (0.0, 0.0, 0.0))
+        phi = [mb.state(f"rope.joint_{i+1}.phi[{k+1}]", a0[k]) for k in range(3)]
+        phid = [mb.state(f"rope.joint_{i+1}.phid[{k+1}]", 0.0) for k in range(3)]
+        fr = mech.spherical(fr, phi, phid, d=d_joint)
+        if i < n_links:
+            mech.body(fr, mi, tuple(li / 2 * dirv), air_resistance=air)
+            sl = mb.state(f"rope.flexibility_{i+1}.s", li)
+            vl = mb.state(f"rope.flexibility_{i+1}.v", 0.0)
+            fr = mech.prismatic(fr, tuple(dirv), sl, vl, f_applied=-(ci * (sl - li) + di * vl),
+                                name=f"flexibility_{i+1}")
+    mech.body(fr, m_body, (0.0, 0.0, 0.0))
+    for k in range(3):
+        mb.observed[f"body.r_0[{k+1}]"] = fr.r0[k].n
+    mech.solve_accelerations()
+    return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+
+
 def fourbar_planar() -> ReducedSystem:
     """Planar loop of docs/src/examples/kinematic_loops.md:38-80: four bars of length 1.5, five
     revolute joints about z (two of them at the world origin), the loop closed by
@@ -340,6 +378,7 @@ MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "free_couple": free_couple,
     "furuta": furuta,
     "planar_pendulum": planar_pendulum,
+    "rope3e": rope_elastic,
 }
 _cache: Dict[str, ReducedSystem] = {}
 

@@ -2,10 +2,10 @@
  * Model table; one translation unit per model (mbo_model_<name>.c). */
 #include <string.h>
 #include "mbo.h"
-extern const mbo_model mbo_model_pendulum, mbo_model_spring_damper, mbo_model_robot6dof, mbo_model_fourbar, mbo_model_rope6, mbo_model_three_springs, mbo_model_fourbar_planar, mbo_model_free_couple, mbo_model_furuta, mbo_model_planar_pendulum;
+extern const mbo_model mbo_model_pendulum, mbo_model_spring_damper, mbo_model_robot6dof, mbo_model_fourbar, mbo_model_rope6, mbo_model_three_springs, mbo_model_fourbar_planar, mbo_model_free_couple, mbo_model_furuta, mbo_model_planar_pendulum, mbo_model_rope3e;
 static const mbo_model* const MODELS[] = {&mbo_model_pendulum, &mbo_model_spring_damper, &mbo_model_robot6dof,
                                           &mbo_model_fourbar, &mbo_model_rope6, &mbo_model_three_springs,
-                                          &mbo_model_fourbar_planar, &mbo_model_free_couple, &mbo_model_furuta, &mbo_model_planar_pendulum};
+                                          &mbo_model_fourbar_planar, &mbo_model_free_couple, &mbo_model_furuta, &mbo_model_planar_pendulum, &mbo_model_rope3e};
 
 const mbo_model* mbo_find_model(const char* name) {
   for (unsigned i = 0; i < sizeof(MODELS) / sizeof(MODELS[0]); i++)

@@ -138,3 +138,41 @@ def rope_energy(u, m_body, n_links=6, l=1.0, m_rope=6.0, dirv=(0.05, 1.0, 0.0)):
         w = np.array([Wm[2, 1], Wm[0, 2], Wm[1, 0]])
         E += 0.5 * m * v @ v + 0.5 * 0.001 * w @ w + m * 9.80665 * c[1]
     return E
+
+
+def elastic_rope_energy(u, names, p, pnames, n_links=3, l=1.0, m_rope=5.0, dirv=(0.0, -1.0, 0.0)):
+    """Total mechanical energy (kinetic + gravity + link springs) of the flexible rope of
+    test/basic_tests.jl:928-959 from its named states; velocities by differencing an independent
+    numpy forward kinematics along the state velocity."""
+    dirv = np.asarray(dirv, float) / np.linalg.norm(dirv)
+    li, mi = l / n_links, m_rope / n_links
+    ix = {nm: k for k, nm in enumerate(names)}
+    par = {nm: p[k] for k, nm in enumerate(pnames)}
+    ci = n_links * par["rope.c"]
+
+    def unpack(vec_of):
+        phis = [[vec_of(f"rope.joint_{i+1}.phi[{k+1}]", f"rope.joint_{i+1}.phid[{k+1}]") for k in range(3)] for i in range(n_links + 1)]
+        ss = [vec_of(f"rope.flexibility_{i+1}.s", f"rope.flexibility_{i+1}.v") for i in range(n_links)]
+        return phis, ss
+
+    def fk(eps):
+        phis, ss = unpack(lambda q, v: u[ix[q]] + eps * u[ix[v]])
+        T, pos, out = np.eye(3), np.zeros(3), []
+        for i in range(n_links + 1):
+            a = phis[i]
+            T = T @ _axis_rot_T(1, a[0]) @ _axis_rot_T(2, a[1]) @ _axis_rot_T(3, a[2])
+            if i < n_links:
+                out.append((mi, pos + T @ (li / 2 * dirv), T.copy()))
+                pos = pos + T @ (ss[i] * dirv)
+            else:
+                out.append((par["body.m"], pos.copy(), T.copy()))
+        return out, ss
+    eps = 1e-6
+    (b0, s0), (bp, _), (bm, _) = fk(0.0), fk(eps), fk(-eps)
+    E = sum(0.5 * ci * (s - li) ** 2 for s in s0)
+    for (m, c, T), (_, cp, Tp), (_, cm, Tm) in zip(b0, bp, bm):
+        v = (cp - cm) / (2 * eps)
+        Wm = ((Tp - Tm) / (2 * eps)) @ T.T
+        w = np.array([Wm[2, 1], Wm[0, 2], Wm[1, 0]])
+        E += 0.5 * m * v @ v + 0.5 * 0.001 * w @ w + m * 9.80665 * c[1]
+    return E

@@ -43,7 +43,7 @@ def _compare(sol, ref, rtol=RTOL):
     assert abs(ga.mean() - oa.mean()) <= 0.02 * oa.mean() + 2
 
 
-@pytest.mark.parametrize("config,N", [("C1", 1024), ("C2", 2048), ("C2B", 1024), ("C3", 1024), ("C3P", 1024), ("C4", 256), ("C5", 128)])
+@pytest.mark.parametrize("config,N", [("C1", 1024), ("C2", 2048), ("C2B", 1024), ("C3", 1024), ("C3P", 1024), ("C4", 256), ("C5", 128), ("C5E", 256)])
 def test_config_parity(oracle, config, N):
     spec = ensembles.make_ensemble(config, N)
     _compare(_run_gpu(spec), _run_oracle(oracle, spec))
