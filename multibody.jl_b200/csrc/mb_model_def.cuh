@@ -42,10 +42,19 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
   mbk::rosenbrock_rows_kernel<MODEL, typename mbk::TabOf<ALG>::type, BLOCK, MINB>
 #endif
 
+#if defined(MB_RODAS_CLASSIC) || !MB_ROWS_SMEM
+#define MB_ROWS_SMEM_BYTES(N, BLOCK) 0
+#else
+#define MB_ROWS_SMEM_BYTES(N, BLOCK) (2 * (N) * sizeof(double) * (BLOCK))
+#endif
+// shared-memory carve-out in percent of the 228 KB maximum: what the kernel needs, the rest stays L1
+static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 233471) / 233472) : 0; }
+
 #define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
   struct MbModel_##X {                                                                              \
     static constexpr int N = MBM_##X##_N, NP = MBM_##X##_M, NLU = MBM_##X##_NLU,                    \
-                         HAS_DT = MBM_##X##_HAS_DT, IS_ODE = MBM_##X##_IS_ODE;                      \
+                         HAS_DT = MBM_##X##_HAS_DT, IS_ODE = MBM_##X##_IS_ODE,                      \
+                         SLOTS = MBM_##X##_SMEM_SLOTS;                                              \
     static __device__ __forceinline__ void rhs(const double* u, const double* p, double t,         \
                                                const double* tb, double* du) {                      \
       mbm_##X##_rhs(u, p, t, tb, du);                                                               \
@@ -70,11 +79,12 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
   };                                                                                                \
   static cudaError_t mb_launch_##X(int alg, const MbArgs& a, int sm_count, cudaStream_t st) {       \
     int bps = 1;                                                                                    \
-    const size_t smem = (size_t)MBM_##X##_SMEM_SLOTS * sizeof(double) * BLOCK;                      \
+    const size_t smem0 = (size_t)MBM_##X##_SMEM_SLOTS * sizeof(double) * BLOCK;                     \
+    size_t smem = smem0;                                                                            \
     if (alg == 1) {                                                                                 \
       auto kern = mbk::ensemble_kernel<MbModel_##X, 1, BLOCK, MINB, UNR>;                           \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
-      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \
       bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
@@ -82,9 +92,10 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 2) {                                                                          \
+      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, BLOCK);                                \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, 2, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
-      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \
       bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \
@@ -92,9 +103,10 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 3) {                                                                          \
+      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, BLOCK);                                \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, 3, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
-      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, smem ? 100 : 0);   \
+      cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \
       cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                       \
       bps = mb_cap_ctas_per_sm(bps);                                                                \
       long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                   \

@@ -1,4 +1,7 @@
 // Kernel set of model 'robot6dof' (generated/mbm_robot6dof.h is emitted by codegen/generate.py).
+#ifndef MB_ROWS_SMEM
+#define MB_ROWS_SMEM 1   // C-sum and df/dt rows in shared memory (profiles/r01_robot_v8_summary.md)
+#endif
 #include "mb_model_def.cuh"
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__

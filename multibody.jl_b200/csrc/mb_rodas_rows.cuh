@@ -8,8 +8,16 @@
 // first version the stage state, the C-sum and the right-hand side output (3 x 36 doubles =
 // 216 of the 255 registers) were live in registers across the inlined rhs(), which left its
 // 2 400-flop body ~40 registers: 300 LDL + 155 STL of spill code, executed 8 times per step.
+//
+// MB_ROWS_SMEM = 1 (set by the model's translation unit) moves the two rows that are written once
+// and read back per stage or per step -- the C-sum `sc` and df/dt -- from local memory to shared
+// memory, laid out [component][thread] (conflict-free): 2 N doubles per thread (147 KB for the
+// robot's 256-thread CTA), ~20 % of the step's thread-local DRAM traffic.
 #pragma once
 #include "mb_ensemble.cuh"
+#ifndef MB_ROWS_SMEM
+#define MB_ROWS_SMEM 0
+#endif
 
 namespace mbk {
 
@@ -30,6 +38,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const dT = &W[R_DT][0];
   double* const p = &W[R_P][0];
   double* const LU = &W[R_LU][0];
+  constexpr bool SROWS = MB_ROWS_SMEM != 0;
+  double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
   long long traj = -1, iter = 0;
   int is = 0, naccept = 0, nreject = 0, nf = 0, njac = 0, nsolve = 0;
@@ -82,7 +92,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
       const double cW = 1.0 / (dt * T::GAMMA);
       M::factor(u, p, t, tb, cW, LU);
       njac++;
-      if (M::HAS_DT) M::dT(u, p, t, tb, dT);
+      if (M::HAS_DT) {
+        M::dT(u, p, t, tb, dT);
+        if (SROWS) {
+#pragma unroll
+          for (int i = 0; i < N; i++) srow[(size_t)(N + i) * BLOCK] = dT[i];
+        }
+      }
       const double inv_dt = 1.0 / dt;
 #pragma unroll 1
       for (int s = 0; s < NST; s++) {
@@ -101,7 +117,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             }
           }
 #pragma unroll
-          for (int i = 0; i < N; i++) { us[i] = x[i]; sc[i] = y[i]; }
+          for (int i = 0; i < N; i++) {
+            us[i] = x[i];
+            if (SROWS) srow[(size_t)i * BLOCK] = y[i]; else sc[i] = y[i];
+          }
         }
         M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
         {
@@ -110,8 +129,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = W[s][i];
-            if (M::HAS_DT) v = fma(dd, dT[i], v);
-            if (M::isdiff(i)) v = fma(sc[i], inv_dt, v);
+            if (M::HAS_DT) v = fma(dd, SROWS ? srow[(size_t)(N + i) * BLOCK] : dT[i], v);
+            if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
           M::solve(LU, cW, p, r);
