@@ -254,6 +254,17 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     pr.smem_slots, pr.reg_target = slots, int(sys.meta.get("reg_target", 72))
     out.append(pr.function(f"MB_FN_RHS void mbm_{X}_rhs({args}, double* MB_RESTRICT du)",
                            [(f"du[{i}]", sys.rhs[i]) for i in range(n)]))
+    if sys.meta.get("strided_rhs"):
+        # second copy of the right-hand side reading its state from shared memory laid out
+        # [component][thread] (u points at this thread's column): the stage state of the
+        # Rosenbrock row kernel (csrc/mb_rodas_rows.cuh, MB_ROWS_SMEM = 2)
+        pr.input_fmt = dict(fmt, u="u[{i} * MB_S_STRIDE]")
+        out.append("#ifdef MB_RHS_STRIDED")
+        out.append(pr.function(f"MB_FN_RHS void mbm_{X}_rhs_s(const double* u, const double* MB_RESTRICT p, double t, "
+                               f"const double* MB_RESTRICT tb, double* MB_RESTRICT du)",
+                               [(f"du[{i}]", sys.rhs[i]) for i in range(n)]))
+        out.append("#endif")
+        pr.input_fmt = fmt
     pr.smem_slots = 0
     out.append("")
     out.append(pr.function(f"MB_FN void mbm_{X}_jac({args}, double* MB_RESTRICT Jnz)",

@@ -45,7 +45,13 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #if defined(MB_RODAS_CLASSIC) || !MB_ROWS_SMEM
 #define MB_ROWS_SMEM_BYTES(N, BLOCK) 0
 #else
-#define MB_ROWS_SMEM_BYTES(N, BLOCK) (2 * (N) * sizeof(double) * (BLOCK))
+#define MB_ROWS_SMEM_BYTES(N, BLOCK) ((MB_ROWS_SMEM == 2 ? 3 : 2) * (N) * sizeof(double) * (BLOCK))
+#endif
+// rhs_s: right-hand side reading a [component][thread]-strided state (generated under MB_RHS_STRIDED)
+#ifdef MB_RHS_STRIDED
+#define MB_RHS_S_NAME(X) mbm_##X##_rhs_s
+#else
+#define MB_RHS_S_NAME(X) mbm_##X##_rhs
 #endif
 // shared-memory carve-out in percent of the 228 KB maximum: what the kernel needs, the rest stays L1
 static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 233471) / 233472) : 0; }
@@ -58,6 +64,10 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
     static __device__ __forceinline__ void rhs(const double* u, const double* p, double t,         \
                                                const double* tb, double* du) {                      \
       mbm_##X##_rhs(u, p, t, tb, du);                                                               \
+    }                                                                                               \
+    static __device__ __forceinline__ void rhs_s(const double* u, const double* p, double t,       \
+                                                 const double* tb, double* du) {                    \
+      MB_RHS_S_NAME(X)(u, p, t, tb, du);                                                            \
     }                                                                                               \
     static __device__ __forceinline__ void dT(const double* u, const double* p, double t,          \
                                               const double* tb, double* o) {                        \

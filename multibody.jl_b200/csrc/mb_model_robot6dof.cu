@@ -1,6 +1,9 @@
 // Kernel set of model 'robot6dof' (generated/mbm_robot6dof.h is emitted by codegen/generate.py).
 #ifndef MB_ROWS_SMEM
-#define MB_ROWS_SMEM 1   // C-sum and df/dt rows in shared memory (profiles/r01_robot_v8_summary.md)
+#define MB_ROWS_SMEM 1   // C-sum and df/dt rows in shared memory; 2 (stage state too) measured 3 % slower (profiles/r01_robot_v8_summary.md)
+#endif
+#if MB_ROWS_SMEM == 2
+#define MB_RHS_STRIDED
 #endif
 #include "mb_model_def.cuh"
 #define MB_FN static __device__ __forceinline__

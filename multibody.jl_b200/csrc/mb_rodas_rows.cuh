@@ -12,7 +12,9 @@
 // MB_ROWS_SMEM = 1 (set by the model's translation unit) moves the two rows that are written once
 // and read back per stage or per step -- the C-sum `sc` and df/dt -- from local memory to shared
 // memory, laid out [component][thread] (conflict-free): 2 N doubles per thread (147 KB for the
-// robot's 256-thread CTA), ~20 % of the step's thread-local DRAM traffic.
+// robot's 256-thread CTA), ~20 % of the step's thread-local DRAM traffic.  MB_ROWS_SMEM = 2 also
+// keeps the stage state `us` there; the model then provides rhs_s(), a copy of the right-hand
+// side that reads its state with the [component][thread] stride (MB_RHS_STRIDED).
 #pragma once
 #include "mb_ensemble.cuh"
 #ifndef MB_ROWS_SMEM
@@ -38,7 +40,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const dT = &W[R_DT][0];
   double* const p = &W[R_P][0];
   double* const LU = &W[R_LU][0];
-  constexpr bool SROWS = MB_ROWS_SMEM != 0;
+  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2;
+#define MB_US(i) (*(SUS ? &srow[(size_t)(2 * N + (i)) * BLOCK] : &us[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
   long long traj = -1, iter = 0;
@@ -118,11 +121,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
           }
 #pragma unroll
           for (int i = 0; i < N; i++) {
-            us[i] = x[i];
+            MB_US(i) = x[i];
             if (SROWS) srow[(size_t)i * BLOCK] = y[i]; else sc[i] = y[i];
           }
         }
-        M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
+        if (SUS) M::rhs_s(srow + (size_t)2 * N * BLOCK, p, t + T::CT(s) * dt, tb, &W[s][0]);
+        else M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
         {
           double r[N];
           const double dd = dt * T::D(s);
@@ -145,7 +149,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         double sacc = 0.0;
 #pragma unroll
         for (int i = 0; i < N; i++) {
-          const double k8 = W[NST - 1][i], ua = u[i], ub = us[i] + k8;
+          const double k8 = W[NST - 1][i], ua = u[i], ub = MB_US(i) + k8;
           const double scl = a.abstol + fmax(fabs(ua), fabs(ub)) * a.reltol;
           const double q = k8 / scl;
           sacc += q * q;
@@ -170,7 +174,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             double* __restrict__ o = a.out_u + (size_t)is * N * a.N + traj;
             if (ts == tn) {
 #pragma unroll
-              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = us[i] + W[NST - 1][i];
+              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = MB_US(i) + W[NST - 1][i];
             } else {
               const double th = (ts - t) / dt;
               for (int i = 0; i < N; i++) {
@@ -180,14 +184,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
                   const double kj = W[j][i];
                   K1 = fma(T::H(0, j), kj, K1); K2 = fma(T::H(1, j), kj, K2); K3 = fma(T::H(2, j), kj, K3);
                 }
-                const double un = us[i] + W[NST - 1][i];
+                const double un = MB_US(i) + W[NST - 1][i];
                 o[(size_t)i * a.N] = (1.0 - th) * u[i] + th * (un + (1.0 - th) * (K1 + th * (K2 + th * K3)));
               }
             }
             is++;
           }
 #pragma unroll
-          for (int i = 0; i < N; i++) u[i] = us[i] + W[NST - 1][i];
+          for (int i = 0; i < N; i++) u[i] = MB_US(i) + W[NST - 1][i];
           t = tn;
           qold = fmax(EEst, QOLDINIT);
           dt = fmin(dt / q, dtmax);
@@ -210,5 +214,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
     }
   }
 }
+
+#undef MB_US
 
 }  // namespace mbk

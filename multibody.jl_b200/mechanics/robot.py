@@ -189,6 +189,7 @@ def robot6dof() -> ReducedSystem:
     # dependency chains, 2 warps per scheduler), so it is off (0 slots) by default.
     return mb.finish(tspan=(0.0, 2.0), mechanism=mech,
                      smem_slots=int(os.environ.get("MB_ROBOT_SLOTS", "0")),
+                     strided_rhs=True,
                      reg_target=int(os.environ.get("MB_ROBOT_RTARGET", "72")),
                      stage_factor=os.environ.get("MB_ROBOT_STAGE_FACTOR", "1") == "1")
 
