@@ -43,9 +43,9 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #endif
 
 #if defined(MB_RODAS_CLASSIC) || !MB_ROWS_SMEM
-#define MB_ROWS_SMEM_BYTES(N, BLOCK) 0
+#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) 0
 #else
-#define MB_ROWS_SMEM_BYTES(N, BLOCK) ((MB_ROWS_SMEM == 2 ? 3 : 2) * (N) * sizeof(double) * (BLOCK))
+#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((1 + ((HASDT) ? 1 : 0) + (MB_ROWS_SMEM == 2 ? 1 : 0)) * (N) * sizeof(double) * (BLOCK))
 #endif
 // rhs_s: right-hand side reading a [component][thread]-strided state (generated under MB_RHS_STRIDED)
 #ifdef MB_RHS_STRIDED
@@ -102,7 +102,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 2) {                                                                          \
-      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, BLOCK);                                \
+      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, MBM_##X##_HAS_DT, BLOCK);                                \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, 2, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \
@@ -113,7 +113,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 3) {                                                                          \
-      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, BLOCK);                                \
+      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, MBM_##X##_HAS_DT, BLOCK);                                \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, 3, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \

@@ -41,7 +41,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const p = &W[R_P][0];
   double* const LU = &W[R_LU][0];
   constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2;
-#define MB_US(i) (*(SUS ? &srow[(size_t)(2 * N + (i)) * BLOCK] : &us[i]))
+  constexpr int S_DT = N, S_US = (M::HAS_DT ? 2 : 1) * N;     // shared rows: sc | df/dt (if any) | us (mode 2)
+#define MB_US(i) (*(SUS ? &srow[(size_t)(S_US + (i)) * BLOCK] : &us[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
   long long traj = -1, iter = 0;
@@ -99,7 +100,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         M::dT(u, p, t, tb, dT);
         if (SROWS) {
 #pragma unroll
-          for (int i = 0; i < N; i++) srow[(size_t)(N + i) * BLOCK] = dT[i];
+          for (int i = 0; i < N; i++) srow[(size_t)(S_DT + i) * BLOCK] = dT[i];
         }
       }
       const double inv_dt = 1.0 / dt;
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             if (SROWS) srow[(size_t)i * BLOCK] = y[i]; else sc[i] = y[i];
           }
         }
-        if (SUS) M::rhs_s(srow + (size_t)2 * N * BLOCK, p, t + T::CT(s) * dt, tb, &W[s][0]);
+        if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, &W[s][0]);
         else M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
         {
           double r[N];
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = W[s][i];
-            if (M::HAS_DT) v = fma(dd, SROWS ? srow[(size_t)(N + i) * BLOCK] : dT[i], v);
+            if (M::HAS_DT) v = fma(dd, SROWS ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
