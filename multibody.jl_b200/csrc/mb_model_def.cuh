@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #if defined(MB_RODAS_CLASSIC) || !MB_ROWS_SMEM
 #define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) 0
 #else
-#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((1 + ((HASDT) ? 1 : 0) + (MB_ROWS_SMEM == 2 ? 1 : 0)) * (N) * sizeof(double) * (BLOCK))
+#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((1 + (((HASDT) && MB_ROWS_SMEM != 3) ? 1 : 0) + (MB_ROWS_SMEM == 2 ? 1 : 0)) * (N) * sizeof(double) * (BLOCK))
 #endif
 // rhs_s: right-hand side reading a [component][thread]-strided state (generated under MB_RHS_STRIDED)
 #ifdef MB_RHS_STRIDED

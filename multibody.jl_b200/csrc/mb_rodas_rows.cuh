@@ -41,7 +41,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const p = &W[R_P][0];
   double* const LU = &W[R_LU][0];
   constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2;
-  constexpr int S_DT = N, S_US = (M::HAS_DT ? 2 : 1) * N;     // shared rows: sc | df/dt (if any) | us (mode 2)
+  constexpr bool SDT = SROWS && MB_ROWS_SMEM != 3 && M::HAS_DT;            // mode 3: only the C-sum row
+  constexpr int S_DT = N, S_US = (SDT ? 2 : 1) * N;     // shared rows: sc | df/dt (if any) | us (mode 2)
 #define MB_US(i) (*(SUS ? &srow[(size_t)(S_US + (i)) * BLOCK] : &us[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
@@ -98,7 +99,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
       njac++;
       if (M::HAS_DT) {
         M::dT(u, p, t, tb, dT);
-        if (SROWS) {
+        if (SDT) {
 #pragma unroll
           for (int i = 0; i < N; i++) srow[(size_t)(S_DT + i) * BLOCK] = dT[i];
         }
@@ -134,7 +135,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = W[s][i];
-            if (M::HAS_DT) v = fma(dd, SROWS ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
+            if (M::HAS_DT) v = fma(dd, SDT ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
