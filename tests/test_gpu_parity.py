@@ -241,3 +241,24 @@ def test_device_result_equals_reference_run_output():
     assert api.successful_retcode(sol)
     assert np.abs(sol.u[0, 0, :] - case["rod_frame_a_phi_t1"]).max() < 1e-4
     assert np.abs(sol.u[1, 0, :] - case["rod_frame_a_phi_t2"]).max() < case["atol"]
+
+
+def test_full_size_c3_and_quarter_size_c4_are_scheduling_independent():
+    """Size-independent properties at BASELINE sizes.  C3 at its full 262 144 trajectories and C4 at
+    262 144 (a quarter of 1 Mi; the full size is what bench.py runs): every trajectory succeeds; a
+    slice of the big run equals, bit for bit, the same trajectories solved as a small ensemble of
+    their own (a trajectory's arithmetic does not depend on the ensemble size, on which thread
+    picked it from the work queue or on its CTA neighbours); and the on-device ensemble statistic
+    equals the host sum of the saved states (checksum of the whole output)."""
+    for config, N, lo, cnt in (("C3", 1 << 18, 200000, 512), ("C4", 1 << 18, 131072, 256)):
+        spec = ensembles.make_ensemble(config, N)
+        sol = _run_gpu(spec, reduction=True)
+        assert np.all(sol.retcode == 1), config
+        assert sol.reduction["count"] == N
+        np.testing.assert_allclose(sol.reduction["sum"], sol.u.sum(axis=2), rtol=1e-9, atol=1e-7)
+        small = ensembles.make_ensemble(config, cnt, offset=lo)
+        assert np.array_equal(small.u0, spec.u0[:, lo:lo + cnt]) and np.array_equal(small.p, spec.p[:, lo:lo + cnt])
+        sub = _run_gpu(small)
+        assert np.array_equal(sub.u, sol.u[:, :, lo:lo + cnt]), config
+        assert np.array_equal(sub.stats, sol.stats[:, lo:lo + cnt]), config
+        del sol, sub
