@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define MBB200_ABI_VERSION 1
+#define MBB200_ABI_VERSION 2
 
 /* algorithm ids (OrdinaryDiffEq names: Tsit5(), Rodas5P(), Rodas4()) */
 enum { MBB200_ALG_TSIT5 = 1, MBB200_ALG_RODAS5P = 2, MBB200_ALG_RODAS4 = 3 };
@@ -55,6 +55,14 @@ typedef struct mbb200_opts {
   double dtmin;       /* 0 = default                                                    */
   double dtmax;       /* 0 = t1 - t0                                                    */
   int64_t maxiters;   /* 0 = 100000                                                     */
+  /* PI-controller details of OrdinaryDiffEq (ABI version 2):
+   * dead band of `step_accept_controller!`: when qsteady_min <= q <= qsteady_max the step size
+   * is kept.  0, 0 = the method's default: (1, 1) for Tsit5, (1, 6/5) for the Rosenbrock methods
+   * (`qsteady_max_default(::OrdinaryDiffEqAdaptiveImplicitAlgorithm)`). */
+  double qsteady_min, qsteady_max;
+  int32_t pow_mode;   /* 0 = `fastpower` of the reference's controller (Float32 exp2 of an          */
+                      /* approximate log2), 1 = exact double-precision pow                         */
+  int32_t reserved;   /* must be 0                                                                 */
 } mbb200_opts;
 
 #define MBB200_FLAG_REDUCE 1

@@ -33,7 +33,9 @@ SYMBOLS = [
 class Opts(C.Structure):
     _fields_ = [("alg", C.c_int32), ("flags", C.c_int32), ("t0", C.c_double), ("t1", C.c_double),
                 ("abstol", C.c_double), ("reltol", C.c_double), ("dt0", C.c_double),
-                ("dtmin", C.c_double), ("dtmax", C.c_double), ("maxiters", C.c_int64)]
+                ("dtmin", C.c_double), ("dtmax", C.c_double), ("maxiters", C.c_int64),
+                ("qsteady_min", C.c_double), ("qsteady_max", C.c_double), ("pow_mode", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 class ImageHeader(C.Structure):

@@ -226,14 +226,18 @@ def shutdown():
         _devices = None
 
 
-def make_opts(alg, tspan, abstol=1e-6, reltol=1e-3, dt=0.0, dtmin=0.0, dtmax=0.0, maxiters=0, reduce=False):
+def make_opts(alg, tspan, abstol=1e-6, reltol=1e-3, dt=0.0, dtmin=0.0, dtmax=0.0, maxiters=0, reduce=False,
+              qsteady_min=0.0, qsteady_max=0.0, exact_pow=False):
+    """`qsteady_min/max` are OrdinaryDiffEq's solve keywords of the same name (0, 0 = the method's
+    default: (1, 1) Tsit5, (1, 6/5) Rosenbrock); `exact_pow` replaces the controller's `fastpower`."""
     return _lib.Opts(alg.id, _lib.FLAG_REDUCE if reduce else 0, tspan[0], tspan[1], abstol, reltol,
-                     dt, dtmin, dtmax, int(maxiters))
+                     dt, dtmin, dtmax, int(maxiters), qsteady_min, qsteady_max, 1 if exact_pow else 0, 0)
 
 
 def solve(eprob: Union[EnsembleProblem, ODEProblem], alg, ensemblealg: Optional[EnsembleB200] = None, *,
           trajectories: int = 1, saveat=None, abstol: float = 1e-6, reltol: float = 1e-3, dt: float = 0.0,
-          dtmin: float = 0.0, dtmax: float = 0.0, maxiters: int = 0, reduction: bool = False) -> EnsembleSolution:
+          dtmin: float = 0.0, dtmax: float = 0.0, maxiters: int = 0, reduction: bool = False,
+          qsteady_min: float = 0.0, qsteady_max: float = 0.0, exact_pow: bool = False) -> EnsembleSolution:
     """`solve(eprob, alg, EnsembleB200(); trajectories, saveat, abstol, reltol, ...)`.
     Defaults are SciML's (abstol 1e-6, reltol 1e-3).  A plain ODEProblem is run as an
     ensemble of one.  `reduction=True` also returns count/mean/variance statistics."""
@@ -252,7 +256,7 @@ def solve(eprob: Union[EnsembleProblem, ODEProblem], alg, ensemblealg: Optional[
     rc = np.zeros(N, np.int32)
     st = np.zeros((5, N), np.int32)
     red = np.zeros(2 * ns * n + 1) if reduction else None
-    o = make_opts(alg, tspan, abstol, reltol, dt, dtmin, dtmax, maxiters, reduction)
+    o = make_opts(alg, tspan, abstol, reltol, dt, dtmin, dtmax, maxiters, reduction, qsteady_min, qsteady_max, exact_pow)
     _lib.check(_lib.lib().mbb200_solve(h.handle, C.byref(o), N, _lib.ptr(U), _lib.ptr(P) if sys.m else None,
                                        _lib.ptr(sv), ns, _lib.ptr(out), _lib.ptr(tf), _lib.ptr(rc), _lib.ptr(st),
                                        _lib.ptr(red) if reduction else None))

@@ -89,6 +89,27 @@ static __constant__ double RD_H[3][8] = {
 constexpr double SAFETY = 0.9, QMIN = 0.2, QMAX = 10.0,
                  QOLDINIT = 1e-4;
 
+// `fastpower` of the reference's PI controller (FastPower.jl, formerly DiffEqBase.fastpow):
+// Float32 exp2 of y times an approximate log2 (rational fit on the significand, D. Goldberg,
+// "Fast approximate logarithms III", table 2 line 8).  Relative error ~1e-5 in the step-size
+// factor; restated so that step sequences follow the reference's, not just converged solutions.
+__device__ __forceinline__ float mb_fastlog2(float x) {
+  const float a = 0.338953f, b = 2.198599f, c = 1.523692f;
+  const unsigned ux1i = __float_as_uint(x);
+  const unsigned ex = (ux1i & 0x7F800000u) >> 23;
+  const bool greater = (ux1i & 0x00400000u) != 0u;
+  float signif = __uint_as_float((ux1i & 0x007FFFFFu) | (greater ? 0x3f000000u : 0x3f800000u));
+  const float fexp = __fsub_rn((float)ex, greater ? 126.0f : 127.0f);
+  signif = __fsub_rn(signif, 1.0f);
+  // no FMA contraction: the CPU restatement (oracle, -ffp-contract=off) rounds each operation
+  return __fadd_rn(fexp, __fdiv_rn(__fmul_rn(signif, __fadd_rn(__fmul_rn(a, signif), b)), __fadd_rn(signif, c)));
+}
+__device__ __forceinline__ double mb_ctl_pow(double x, double y, int pow_mode) {
+  if (pow_mode == 1) return pow(x, y);
+  if (x == 0.0) return 0.0;
+  return (double)exp2f(__fmul_rn((float)y, mb_fastlog2((float)x)));
+}
+
 enum { RC_DEFAULT = 0, RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6 };
 
 }  // namespace mbk
@@ -108,6 +129,8 @@ struct MbArgs {
   unsigned long long* queue; // work counter (trajectory index dispenser)
   double t0, t1, abstol, reltol, dt0, dtmin, dtmax;
   long long maxiters;
+  double qs_min, qs_max;     // dead band of the PI controller (step kept when qs_min <= q <= qs_max)
+  int pow_mode;              // 0 fastpower (reference), 1 exact pow
 };
 
 // ---- observed-variable evaluation (the step after the solve: `sol(t, idxs = expr)`) ----------

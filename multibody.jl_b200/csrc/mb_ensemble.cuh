@@ -331,8 +331,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
         double q, q11 = 0.0;
         if (EEst == 0.0) q = 1.0 / QMAX;
         else {
-          q11 = pow(EEst, BETA1);
-          q = q11 / pow(qold, BETA2);
+          q11 = mb_ctl_pow(EEst, BETA1, a.pow_mode);
+          q = q11 / mb_ctl_pow(qold, BETA2, a.pow_mode);
           q = fmax(1.0 / QMAX, fmin(1.0 / QMIN, q / SAFETY));
         }
         if (EEst <= 1.0) {
@@ -379,6 +379,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
           }
           t = tn;
           qold = fmax(EEst, QOLDINIT);
+          if (a.qs_min <= q && q <= a.qs_max) q = 1.0;      // dead band of step_accept_controller!
           dt = fmin(dt / q, dtmax);
           if (!(t < a.t1)) rc = RC_SUCCESS;
         } else {

@@ -164,8 +164,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         double q, q11 = 0.0;
         if (EEst == 0.0) q = 1.0 / QMAX;
         else {
-          q11 = pow(EEst, BETA1);
-          q = q11 / pow(qold, BETA2);
+          q11 = mb_ctl_pow(EEst, BETA1, a.pow_mode);
+          q = q11 / mb_ctl_pow(qold, BETA2, a.pow_mode);
           q = fmax(1.0 / QMAX, fmin(1.0 / QMIN, q / SAFETY));
         }
         if (EEst <= 1.0) {
@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
           for (int i = 0; i < N; i++) u[i] = MB_US(i) + W[NST - 1][i];
           t = tn;
           qold = fmax(EEst, QOLDINIT);
+          if (a.qs_min <= q && q <= a.qs_max) q = 1.0;      // dead band of step_accept_controller!
           dt = fmin(dt / q, dtmax);
           if (!(t < a.t1)) rc = RC_SUCCESS;
         } else {

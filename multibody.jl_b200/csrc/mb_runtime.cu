@@ -266,6 +266,8 @@ static int check_opts(const mbb200_model* m, const mbb200_opts* o, long long N, 
   if (N < 0 || n_save < 0) return fail(MBB200_ERR_BAD_ARG, "negative size");
   if (!(o->abstol > 0.0) || !(o->reltol > 0.0)) return fail(MBB200_ERR_BAD_ARG, "abstol and reltol must be positive");
   if (!(o->t1 >= o->t0)) return fail(MBB200_ERR_BAD_ARG, "tspan must be increasing");
+  if (o->pow_mode != 0 && o->pow_mode != 1) return fail(MBB200_ERR_BAD_ARG, "pow_mode must be 0 (fastpower) or 1 (exact)");
+  if (o->qsteady_min > o->qsteady_max) return fail(MBB200_ERR_BAD_ARG, "qsteady_min > qsteady_max");
   return MBB200_OK;
 }
 
@@ -278,6 +280,8 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
   a.out_u = d_out_u; a.out_tfinal = d_tfinal; a.retcode = d_rc; a.stats = d_stats; a.queue = d.queue;
   a.t0 = o->t0; a.t1 = o->t1; a.abstol = o->abstol; a.reltol = o->reltol; a.dt0 = o->dt0; a.dtmin = o->dtmin;
   a.dtmax = o->dtmax; a.maxiters = o->maxiters;
+  a.qs_min = o->qsteady_min; a.qs_max = o->qsteady_max; a.pow_mode = o->pow_mode;
+  if (a.qs_min == 0.0 && a.qs_max == 0.0) { a.qs_min = 1.0; a.qs_max = (o->alg == MBB200_ALG_TSIT5) ? 1.0 : 1.2; }
   d.last_launches = 0;
   CU(cudaMemsetAsync(d.queue, 0, sizeof(unsigned long long), d.stream));
   CU(cudaEventRecord(d.ev0, d.stream));

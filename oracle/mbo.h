@@ -13,6 +13,12 @@ typedef struct {
   double dt0;         /* 0 = automatic */
   double dtmin, dtmax;/* 0 = default */
   int64_t maxiters;   /* 0 = 100000 */
+  /* step-size dead band of OrdinaryDiffEq's PI controller (`step_accept_controller!`): when
+   * qsteady_min <= q <= qsteady_max the step is kept (q = 1).  Explicit methods: (1, 1);
+   * adaptive implicit / Rosenbrock methods: (1, 6/5).  0, 0 = the method's default. */
+  double qsteady_min, qsteady_max;
+  int32_t pow_mode;   /* 0 = OrdinaryDiffEq's `fastpower` (Float32 exp2 * approximate log2) in the PI controller, 1 = exact pow */
+  int32_t reserved;
 } mbo_opts;
 
 typedef void (*mbo_fn)(const double* u, const double* p, double t, const double* tb, double* out);

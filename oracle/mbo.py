@@ -15,7 +15,9 @@ _lib = None
 class Opts(C.Structure):
     _fields_ = [("alg", C.c_int32), ("jac_mode", C.c_int32), ("abstol", C.c_double),
                 ("reltol", C.c_double), ("dt0", C.c_double), ("dtmin", C.c_double),
-                ("dtmax", C.c_double), ("maxiters", C.c_int64)]
+                ("dtmax", C.c_double), ("maxiters", C.c_int64),
+                ("qsteady_min", C.c_double), ("qsteady_max", C.c_double), ("pow_mode", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 def build(force=False):
@@ -83,7 +85,7 @@ def jac_dense(model, u, p, t, tb):
 
 
 def solve(model, alg, u0, p, tb, tspan, saveat, abstol=1e-6, reltol=1e-3, jac_mode=0,
-          dt0=0.0, dtmin=0.0, dtmax=0.0, maxiters=0, nthreads=1):
+          dt0=0.0, dtmin=0.0, dtmax=0.0, maxiters=0, nthreads=1, qsteady=(0.0, 0.0), pow_mode=0):
     """u0: [n][N], p: [m][N] (SoA).  Returns dict(u=[nsave][n][N], t, retcode, stats=[5][N])."""
     n, m, _ = dims(model)
     u0 = np.ascontiguousarray(u0, dtype=np.float64).reshape(n, -1)
@@ -94,7 +96,7 @@ def solve(model, alg, u0, p, tb, tspan, saveat, abstol=1e-6, reltol=1e-3, jac_mo
     ns = len(saveat)
     out = np.full((ns, n, N), np.nan)
     tf = np.zeros(N); rc = np.zeros(N, np.int32); st = np.zeros((5, N), np.int32)
-    o = Opts(ALG[alg], jac_mode, abstol, reltol, dt0, dtmin, dtmax, maxiters)
+    o = Opts(ALG[alg], jac_mode, abstol, reltol, dt0, dtmin, dtmax, maxiters, qsteady[0], qsteady[1], pow_mode, 0)
     f = lib().mbo_solve_ensemble
     f.argtypes = [C.c_char_p, C.POINTER(Opts), C.c_int64, C.POINTER(C.c_double), C.POINTER(C.c_double),
                   C.POINTER(C.c_double), C.c_double, C.c_double, C.POINTER(C.c_double), C.c_int,

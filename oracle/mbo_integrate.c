@@ -18,6 +18,7 @@
  * held instead by scipy Radau/DOP853 at rtol 1e-12, analytic solutions and convergence order.
  */
 #include <math.h>
+#include <stdio.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -62,6 +63,29 @@ static void f_eval(ctx_t* c, const double* u, double t, double* du) {
   c->md->rhs(u, c->p, t, c->tb, du);
   c->nf++;
 }
+
+/* OrdinaryDiffEq's PI controller raises EEst and qold to beta1 / beta2 with `fastpower`
+ * (FastPower.jl; DiffEqBase.fastpow before it): Float32 exp2 of y times an approximate log2
+ * (rational fit on the significand, D. Goldberg, "Fast approximate logarithms III", table 2 line 8),
+ * so the step-size factors carry a relative error of ~1e-5 -- reproduced here because step sequences,
+ * not just converged solutions, have to match the reference's runs. */
+static float fastlog2f(float x) {
+  const float a = 0.338953f, b = 2.198599f, c = 1.523692f;
+  uint32_t ux1i; memcpy(&ux1i, &x, 4);
+  uint32_t ex = (ux1i & 0x7F800000u) >> 23;
+  uint32_t greater = ux1i & 0x00400000u;
+  uint32_t ux2i; float signif, fexp;
+  if (greater) { ux2i = (ux1i & 0x007FFFFFu) | 0x3f000000u; memcpy(&signif, &ux2i, 4); fexp = (float)ex - 126.0f; }
+  else         { ux2i = (ux1i & 0x007FFFFFu) | 0x3f800000u; memcpy(&signif, &ux2i, 4); fexp = (float)ex - 127.0f; }
+  signif = signif - 1.0f;
+  return fexp + signif * (a * signif + b) / (signif + c);
+}
+static double fastpower(double x, double y) {
+  if (x == 0.0) return 0.0;
+  if (isinf(x) && isinf(y)) return INFINITY;
+  return (double)exp2f((float)y * fastlog2f((float)x));
+}
+static double ctl_pow(const mbo_opts* o, double x, double y) { return o->pow_mode == 1 ? pow(x, y) : fastpower(x, y); }
 
 static double rms_scaled(int n, const double* e, const double* ua, const double* ub, double atol, double rtol) {
   double s = 0.0;
@@ -227,10 +251,13 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
   double dt = (o->dt0 > 0) ? o->dt0 : initial_dt(&c, u, t0, t1, o, order, w1, w2, w3);
   const double beta1 = 7.0 / (10.0 * order), beta2 = 2.0 / (5.0 * order), gam = 0.9, qmin = 0.2, qmax = 10.0;
   double qold = 1e-4;
+  double qs_min = o->qsteady_min, qs_max = o->qsteady_max;
+  if (qs_min == 0.0 && qs_max == 0.0) { qs_min = 1.0; qs_max = rosen ? 1.2 : 1.0; }
   int64_t maxiters = o->maxiters > 0 ? o->maxiters : 100000;
   int64_t iter = 0;
   int rc = RC_SUCCESS;
   int have_fsal = 0;
+  const int trace = getenv("MBO_TRACE") != NULL;
 
   while (t < t1) {
     if (++iter > maxiters) { rc = RC_MAXITERS; break; }
@@ -295,10 +322,11 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
     double q, q11 = 0.0;
     if (EEst == 0.0) q = 1.0 / qmax;
     else {
-      q11 = pow(EEst, beta1);
-      q = q11 / pow(qold, beta2);
+      q11 = ctl_pow(o, EEst, beta1);
+      q = q11 / ctl_pow(o, qold, beta2);
       q = fmax(1.0 / qmax, fmin(1.0 / qmin, q / gam));
     }
+    if (trace) fprintf(stderr, "step t=%.17g dt=%.17g EEst=%.6e q=%.6f %s\n", t, dt, EEst, q, EEst <= 1.0 ? "acc" : "REJ");
     if (EEst <= 1.0) {
       c.naccept++;
       double tn = last ? t1 : t + dt;
@@ -331,6 +359,7 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
       memcpy(u, un, sizeof(double) * n);
       t = tn;
       qold = fmax(EEst, 1e-4);
+      if (qs_min <= q && q <= qs_max) q = 1.0;          /* dead band of step_accept_controller! */
       dt = fmin(dt / q, dtmax);
     } else {
       c.nreject++;

@@ -27,8 +27,8 @@ def test_header_symbols_are_all_exported():
 
 
 def test_abi_version_and_struct_layout():
-    assert _lib.lib().mbb200_abi_version() == 1
-    assert C.sizeof(_lib.Opts) == 72            # 2 x int32 + 7 x double + int64
+    assert _lib.lib().mbb200_abi_version() == 2
+    assert C.sizeof(_lib.Opts) == 96            # 2 x int32 + 7 x double + int64 + 2 x double + 2 x int32
     assert C.sizeof(_lib.ImageHeader) == 72     # 8 + 48 + 2 x int32 + int64
 
 

@@ -310,8 +310,11 @@ def test_planar_loop_constraint_energy_balance(oracle):
     L, m, I33, g, d = 1.5, 1.0, 0.001, 9.80665, 0.1
     # up to t = 1.4: at t ~ 1.54 the parallelogram passes next to its flat (singular) configuration
     sv = np.linspace(0.0, 1.4, 2801)
+    # qsteady (1, 1): at 1e-10 the error estimate of the constraint forces is round-off noise near t = 1.09 and
+    # the Rosenbrock default dead band (1, 6/5) lets the step size collapse into it; the energy balance of the
+    # model, not the controller, is under test here
     r = oracle.solve("fourbar_planar", "rodas5p", s.u0[:, None], s.p0[:, None], s.tables.pack(), (0.0, 1.4), sv,
-                     abstol=1e-10, reltol=1e-10)
+                     abstol=1e-10, reltol=1e-10, qsteady=(1.0, 1.0))
     assert r["retcode"][0] == 1
     u = r["u"][:, :, 0]
     q1, w1, q2, w2, q3, q5 = (u[:, k] for k in range(6))
