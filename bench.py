@@ -41,6 +41,10 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="trajectories in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="tuning runs only: skip the host-buffer leg (the line then has no e2e)")
+    ap.add_argument("--scaling", default="auto", choices=["auto", "strong", "weak"],
+                    help="N > 1: strong = the config's ensemble (1 Mi) sharded over the ranks (BASELINE config 4, default); "
+                         "weak = that many trajectories per rank")
+    ap.add_argument("--dump", default="", help="(reference arm) write the sample's results to this .npz for the parity check")
     return ap.parse_args()
 
 
@@ -121,8 +125,11 @@ def run_reference(args):
         t = time.perf_counter()
         r = mbo.solve(spec.model, spec.alg, spec.u0, spec.p, tb, spec.tspan, spec.saveat, abstol=spec.abstol,
                       reltol=spec.reltol, nthreads=cores)
+        dt_ = time.perf_counter() - t
         assert (r["retcode"] == 1).all()
-        return time.perf_counter() - t
+        if args.dump:
+            np.savez(args.dump, u=r["u"], retcode=r["retcode"], stats=r["stats"])
+        return dt_
     for _ in range(args.warmup):
         step()
     dt = sum(step() for _ in range(args.steps))
@@ -157,13 +164,31 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
+    from multibody_jl_b200 import distributed as mbdist
     spec0 = ensembles.make_ensemble(args.config, 1)
-    N = args.trajectories or spec0.n_total
-    spec = ensembles.make_ensemble(args.config, N, offset=rank * N)
+    scaling = args.scaling if args.scaling != "auto" else "strong"
+    if world == 1:
+        scaling = "weak" if args.scaling == "auto" else scaling       # one GPU: both mean the same run
+    if scaling == "strong":     # the whole ensemble (BASELINE config 4: 1 Mi trajectories) sharded by trajectory index
+        n_job = args.trajectories or spec0.n_total
+        lo, hi = mbdist.shard_range(n_job, rank, world)
+    else:                       # fixed work per GPU
+        n_job = (args.trajectories or spec0.n_total) * world
+        lo, hi = rank * (n_job // world), (rank + 1) * (n_job // world)
+    N = hi - lo
+    spec = ensembles.make_ensemble(args.config, N, offset=lo)
     sys_ = api.multibody(spec.model)
     n, m, ns = sys_.n, sys_.m, len(spec.saveat)
     ens = api.EnsembleB200(devices=[local])
     h = api._ensure(ens, sys_)
+    if world > 1:
+        # the path's only collective runs inside the library (ncclAllReduce behind mbb200_comm_init); torchrun's
+        # rendezvous is used just to hand rank 0's communicator id to the other ranks
+        def bcast(payload):
+            box = [payload]
+            dist.broadcast_object_list(box, src=0)
+            return box[0]
+        mbdist.comm_init(rank, world, bcast)
     flops = h.flops()
     alg = api.Tsit5() if spec.alg == "tsit5" else api.Rodas5P()
     opts = api.make_opts(alg, spec.tspan, spec.abstol, spec.reltol, reduce=True)
@@ -189,9 +214,7 @@ def main():
         _lib.check(L.mbb200_solve_device(h.handle, C.byref(opts), 0, N, d_u0.data_ptr(), d_p.data_ptr(), _lib.ptr(sv), ns,
                                          d_out.data_ptr(), d_tf.data_ptr(), d_rc.data_ptr(), d_st.data_ptr(),
                                          d_red.data_ptr()))
-        ms, nl = _lib.last_timing(0)
-        if world > 1:   # the path's only collective: the ensemble-statistic reduction
-            dist.all_reduce(d_red)
+        ms, nl = _lib.last_timing(0)      # with a communicator d_red now holds the statistic summed over all ranks
         return ms, nl
 
     for _ in range(args.warmup):
@@ -212,7 +235,8 @@ def main():
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     dev_ms_max, wall_ms_max = tms.tolist()
-    value = world * N * args.steps / (dev_ms_max * 1e-3)
+    value = n_job * args.steps / (dev_ms_max * 1e-3)
+    red_count = float(d_red[0].item())          # successful trajectories of the whole job (all-reduced in the library)
 
     rc = d_rc.cpu().numpy()
     stats = d_st.cpu().numpy()
@@ -248,10 +272,6 @@ def main():
     def e2e_step():
         _lib.check(L.mbb200_solve(h.handle, C.byref(opts), N, h_u0.data_ptr(), h_p.data_ptr(), _lib.ptr(sv), ns,
                                   h_out.data_ptr(), h_tf.data_ptr(), h_rc.data_ptr(), h_st.data_ptr(), _lib.ptr(h_red)))
-        if world > 1:
-            r = torch.from_numpy(h_red).to(dev)
-            dist.all_reduce(r)
-            h_red[:] = r.cpu().numpy()
     if not args.no_e2e:
         e2e_step()
     barrier()
@@ -262,24 +282,41 @@ def main():
     e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_val = None if args.no_e2e else world * N * args.steps / e2e_t.item()
+    e2e_val = None if args.no_e2e else n_job * args.steps / e2e_t.item()
     same = None if args.no_e2e else bool(np.array_equal(h_rc.numpy(), rc))
+    # the same call with ordinary pageable buffers (what a Julia Array is): page-locked inside mbb200_solve
+    e2e_pageable = None
+    if not args.no_e2e:
+        g_u0, g_p = np.array(spec.u0), np.array(spec.p)
+        g_out = np.empty((ns, n, N)); g_tf = np.empty(N); g_rc = np.empty(N, np.int32); g_st = np.empty((5, N), np.int32)
+        barrier()
+        t0 = time.perf_counter()
+        _lib.check(L.mbb200_solve(h.handle, C.byref(opts), N, _lib.ptr(g_u0), _lib.ptr(g_p), _lib.ptr(sv), ns,
+                                  _lib.ptr(g_out), _lib.ptr(g_tf), _lib.ptr(g_rc), _lib.ptr(g_st), _lib.ptr(h_red)))
+        barrier()
+        tp = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tp, op=dist.ReduceOp.MAX)
+        e2e_pageable = n_job / tp.item()
+        same = same and bool(np.array_equal(g_rc, rc))
+        del g_out
     h2d = 8 * N * (n + m) + 8 * ns
     d2h = 8 * N * n * ns + N * (8 + 4 + 20) + 8 * (2 * ns * n + 1)
 
     out = {
         "metric": metric_name(spec), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(spec, N), "full_size": N == spec.n_total,
+        "config": {"workload": workload_name(spec, N), "full_size": n_job >= spec.n_total, "trajectories_job": n_job,
                    "l2": "inputs+outputs per step (%.1f GB) exceed the 126 MB L2; no flush needed" % ((h2d + d2h) / 1e9),
-                   "parallelism": f"trajectory shards x{world}, no data-path collective; NCCL all-reduce of ensemble statistics only"},
+                   "parallelism": f"trajectory shards x{world}, no data-path collective; ncclAllReduce of the ensemble statistic inside the library"},
+        "successful_trajectories_job": red_count,
         "wall_ms_per_step": wall_ms_max / args.steps,
         "successful_trajectories": ok, "mean_steps_per_trajectory": float(steps.mean()),
         "mean_rejects_per_trajectory": float(stats[1].mean()),
         "gpu_launches": launches, "clocks": clk,
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "matches_device_run": same},
+                "matches_device_run": same, "host_buffers": "pinned", "pageable_value": e2e_pageable},
         "roofline": {"bound": "fp64", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "TFLOP/s",
                      "frac": achieved / peak, "traffic": traffic,
                      "peak_source": "FP64 DFMA probe measured in this run (MEASURED_PEAKS.json holds HBM/BF16 only)",
@@ -292,8 +329,10 @@ def main():
         # spinning next to the oracle's pthreads); bounded sample of the same workload
         cores = os.cpu_count() or 1
         sample = args.cpu_sample or max(256, 256 * cores)
+        sample = min(sample, N)
+        dump = os.path.join("/tmp", f"mbb200_parity_{os.getpid()}.npz")
         r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--config", args.config,
-                            "--steps", "1", "--warmup", "0", "--cpu-sample", str(sample)],
+                            "--steps", "1", "--warmup", "0", "--cpu-sample", str(sample), "--dump", dump],
                            capture_output=True, text=True, env={k: v for k, v in os.environ.items()
                                                                 if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
         try:
@@ -301,6 +340,19 @@ def main():
         except Exception as e:   # keep the GPU line even if the CPU leg failed
             out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": cores, "kind": "port",
                                    "sample": f"failed: {e}: {r.stderr[-200:]}"}
+        # parity of THIS run: the oracle's sample (first `sample` trajectories of the stream) against the device result
+        try:
+            ref = np.load(dump)
+            gpu_u = d_out[:, :, :sample].cpu().numpy()
+            scale = np.maximum(np.abs(ref["u"]).max(axis=(0, 2), keepdims=True), 1e-3)
+            err = np.abs(gpu_u - ref["u"]) / scale
+            out["parity"] = {"n": int(sample), "max_scaled_err": float(err.max()), "tolerance": 1e-6,
+                             "retcodes_equal": bool(np.array_equal(ref["retcode"], rc[:sample])),
+                             "naccept_gpu_mean": float(stats[0, :sample].mean()), "naccept_oracle_mean": float(ref["stats"][0].mean()),
+                             "against": "oracle (CPU restatement; Rosenbrock path unpinned below 3.5e-4 vs reference-run outputs, profiles/r02_pin_table.md)"}
+            os.remove(dump)
+        except Exception as e:
+            out["parity"] = {"n": 0, "error": str(e)}
     if rank == 0:
         print(json.dumps(out))
     if world > 1:

@@ -35,7 +35,8 @@ enum { MBB200_ALG_TSIT5 = 1, MBB200_ALG_RODAS5P = 2, MBB200_ALG_RODAS4 = 3 };
 /* SciMLBase.ReturnCode values written to retcode[] */
 enum {
   MBB200_RC_DEFAULT = 0, MBB200_RC_SUCCESS = 1, MBB200_RC_DTNAN = 3, MBB200_RC_MAXITERS = 4,
-  MBB200_RC_DTLESSTHANMIN = 5, MBB200_RC_UNSTABLE = 6
+  MBB200_RC_DTLESSTHANMIN = 5, MBB200_RC_UNSTABLE = 6,
+  MBB200_RC_INITIALFAILURE = 7   /* DAE: no consistent algebraic states found for this trajectory */
 };
 
 /* library errors */
@@ -102,7 +103,10 @@ void mbb200_model_free(mbb200_model* model);
  *   out_tfinal[N], retcode [N], stats [5][N] = naccept, nreject, nf, njac, nsolve
  *   reduce_out[2*n_save*n + 1]  count, sum(x), sum(x^2) over successful trajectories
  *                               (nullable; filled when flags & MBB200_FLAG_REDUCE)
- * Trajectories are sharded in contiguous blocks over the initialised devices. */
+ * Trajectories are sharded in contiguous blocks over the initialised devices.  Host buffers may be
+ * ordinary pageable memory: they are page-locked for the duration of the call.  Results are
+ * copied back chunk by chunk while the kernel is still integrating the rest of the ensemble.
+ * Thread-safe: concurrent calls serialise per device. */
 int mbb200_solve(mbb200_model* model, const mbb200_opts* opts, int64_t N,
                  const double* u0, const double* p, const double* saveat, int32_t n_save,
                  double* out_u, double* out_tfinal, int32_t* retcode, int32_t* stats,
@@ -115,6 +119,20 @@ int mbb200_solve_device(mbb200_model* model, const mbb200_opts* opts, int dev_in
                         const double* d_u0, const double* d_p, const double* saveat, int32_t n_save,
                         double* d_out_u, double* d_out_tfinal, int32_t* d_retcode, int32_t* d_stats,
                         double* d_reduce_out);
+
+/* Cross-process ensemble statistics: one process per GPU, the only
+ * collective of the path is the sum of reduce_out over the ranks.  Rank 0 obtains an id with
+ * mbb200_comm_unique_id (128 bytes, a ncclUniqueId), the launcher distributes it (the Julia glue:
+ * through MPI.jl / Distributed.jl / a file; bench.py: through its torchrun rendezvous), every
+ * rank calls mbb200_comm_init after mbb200_init.  From then on mbb200_solve /
+ * mbb200_solve_device (device index 0) with MBB200_FLAG_REDUCE return the statistic summed over
+ * ALL ranks (ncclAllReduce, f64, on the solve stream); every rank must make the call.  NCCL is
+ * bound at run time (libnccl.so.2 already in the process, $MBB200_NCCL_LIB, or the system copy). */
+int mbb200_comm_unique_id(void* id_out, size_t len);
+int mbb200_comm_init(const void* id, size_t len, int rank, int nranks);
+int mbb200_comm_info(int* rank, int* nranks);            /* returns 1 when a communicator is active */
+int mbb200_comm_allreduce(double* host_buf, int64_t count);   /* in-place sum over ranks (no-op without a communicator) */
+void mbb200_comm_destroy(void);
 
 /* Observed (eliminated) variables of saved states -- the `sol(tv, idxs = expr)` read-back every
  * reference assertion goes through (test/test_robot.jl:321-325).  `u` is the

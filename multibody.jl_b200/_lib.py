@@ -27,6 +27,7 @@ SYMBOLS = [
     "mbb200_solve", "mbb200_solve_device", "mbb200_model_observed_count", "mbb200_observed", "mbb200_last_timing", "mbb200_measure_fp64_peak",
     "mbb200_dev_alloc", "mbb200_dev_free", "mbb200_dev_upload", "mbb200_dev_download",
     "mbb200_host_alloc_pinned", "mbb200_host_free_pinned", "mbb200_last_error", "mbb200_shutdown",
+    "mbb200_comm_unique_id", "mbb200_comm_init", "mbb200_comm_info", "mbb200_comm_allreduce", "mbb200_comm_destroy",
 ]
 
 
@@ -87,6 +88,11 @@ def lib() -> C.CDLL:
         L.mbb200_host_alloc_pinned.argtypes = [C.c_size_t, C.POINTER(vp)]
         L.mbb200_host_free_pinned.argtypes = [vp]
         L.mbb200_shutdown.restype = None
+        L.mbb200_comm_unique_id.argtypes = [vp, C.c_size_t]
+        L.mbb200_comm_init.argtypes = [vp, C.c_size_t, C.c_int, C.c_int]
+        L.mbb200_comm_info.argtypes = [ip, ip]
+        L.mbb200_comm_allreduce.argtypes = [vp, C.c_int64]
+        L.mbb200_comm_destroy.restype = None
         _lib = L
     return _lib
 

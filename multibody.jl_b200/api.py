@@ -266,6 +266,6 @@ def solve(eprob: Union[EnsembleProblem, ODEProblem], alg, ensemblealg: Optional[
         ms, nl = max(ms, m_), nl + l_
     redd = None
     if reduction:
-        from .distributed import allreduce_statistics, finalize_statistics
-        redd = finalize_statistics(allreduce_statistics(red), ns, n)   # no-op outside torch.distributed
+        from .distributed import finalize_statistics
+        redd = finalize_statistics(red, ns, n)   # already summed over the ranks of the library communicator, if any
     return EnsembleSolution(sys, sv, out, tf, rc, st, redd, ms, nl, P[:sys.m] if sys.m else None)

@@ -278,12 +278,13 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
                            [(f"obs[{k}]", sys.observed[nm]) for k, nm in enumerate(obs_names)]))
     out.append("")
     pr.smem_slots = slots if sys.meta.get("stage_factor", True) else 0
-    lu_assign = [(f"LU[{s}]", node) for s, node in enumerate(code.lu_nodes)]
+    out.append("#ifndef MB_LU_AT\n#define MB_LU_AT(k) LU[k]   /* slot k of this trajectory's LU storage (a TU may stride it) */\n#endif")
+    lu_assign = [(f"MB_LU_AT({s})", node) for s, node in enumerate(code.lu_nodes)]
     out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     out.append("")
     pr.smem_slots = 0
-    spr = Printer(code.solve_graph, {"lu": "LU[{i}]", "b": "b{i}", "c": "c", "p": "p[{i}]"})
+    spr = Printer(code.solve_graph, {"lu": "MB_LU_AT({i})", "b": "b{i}", "c": "c", "p": "p[{i}]"})
     sol_lines = [f"MB_FN_SOLVE void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "
                  f"double* MB_RESTRICT b) {{"]
     for i in range(n):

@@ -107,10 +107,11 @@ __device__ __forceinline__ float mb_fastlog2(float x) {
 __device__ __forceinline__ double mb_ctl_pow(double x, double y, int pow_mode) {
   if (pow_mode == 1) return pow(x, y);
   if (x == 0.0) return 0.0;
-  return (double)exp2f(__fmul_rn((float)y, mb_fastlog2((float)x)));
+  // exp2 in double, rounded to Float32: bit-identical to the CPU restatement (exp2f implementations differ by an ulp)
+  return (double)(float)exp2((double)__fmul_rn((float)y, mb_fastlog2((float)x)));
 }
 
-enum { RC_DEFAULT = 0, RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6 };
+enum { RC_DEFAULT = 0, RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6, RC_INITIALFAILURE = 7 };
 
 }  // namespace mbk
 
@@ -131,7 +132,25 @@ struct MbArgs {
   long long maxiters;
   double qs_min, qs_max;     // dead band of the PI controller (step kept when qs_min <= q <= qs_max)
   int pow_mode;              // 0 fastpower (reference), 1 exact pow
+  // streamed read-back (mb_runtime.cu): per-chunk counters of retired trajectories; the thread that
+  // completes a chunk of 2^chunk_shift trajectories raises its flag in mapped host memory
+  unsigned* done;            // nullable
+  int* flags;
+  int chunk_shift;
 };
+
+// called by the thread that has just written all results of trajectory `traj`
+__device__ __forceinline__ void mb_retire(const MbArgs& a, long long traj) {
+  if (!a.done) return;
+  __threadfence();                                           // results visible device-wide before the count
+  const long long c = traj >> a.chunk_shift;
+  long long size = a.N - (c << a.chunk_shift);
+  if (size > (1ll << a.chunk_shift)) size = 1ll << a.chunk_shift;
+  if ((long long)atomicAdd(&a.done[c], 1u) + 1 == size) {
+    __threadfence_system();
+    *(volatile int*)&a.flags[c] = 1;
+  }
+}
 
 // ---- observed-variable evaluation (the step after the solve: `sol(t, idxs = expr)`) ----------
 struct MbObsArgs {

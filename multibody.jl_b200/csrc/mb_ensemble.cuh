@@ -155,17 +155,22 @@ __device__ __noinline__ double initial_dt(const double (&u)[M::N], const double*
 template <class M>
 __device__ __noinline__ int dae_init(double* u, const double* p, const double* tb, double t0, double abstol,
                                      double* LU) {
+  // returns the number of right-hand-side evaluations; NEGATIVE when the algebraic residual is
+  // still above tolerance after 10 Newton steps (the caller retires the trajectory with
+  // ReturnCode.InitialFailure instead of integrating from an inconsistent state)
   constexpr int N = M::N;
   const double tol = fmin(abstol, 1e-10);
   int nf = 0;
-  for (int it = 0; it < 10; it++) {
+  bool ok = false;
+  for (int it = 0; it <= 10; it++) {
     double f[N];
     M::rhs(u, p, t0, tb, f);
     nf++;
     double r = 0.0;
 #pragma unroll
     for (int i = 0; i < N; i++) if (!M::isdiff(i)) r = fmax(r, fabs(f[i]));
-    if (!(r > tol)) break;
+    if (!(r > tol)) { ok = true; break; }
+    if (it == 10) break;
     M::factor(u, p, t0, tb, 1e20, LU);
 #pragma unroll
     for (int i = 0; i < N; i++) if (M::isdiff(i)) f[i] = 0.0;
@@ -173,7 +178,7 @@ __device__ __noinline__ int dae_init(double* u, const double* p, const double* t
 #pragma unroll
     for (int i = 0; i < N; i++) if (!M::isdiff(i)) u[i] += f[i];
   }
-  return nf;
+  return ok ? nf : -nf;
 }
 
 }  // namespace mbk
@@ -220,7 +225,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
         for (int i = 0; i < M::NP; i++) p[i] = a.p[(size_t)i * a.N + traj];
         t = a.t0; is = 0; iter = 0; qold = QOLDINIT;
         naccept = nreject = nf = njac = nsolve = 0;
-        if (ROSEN && !M::IS_ODE) nf += dae_init<M>(u, p, tb, a.t0, a.abstol, LU);
+        bool init_fail = false;
+        if (ROSEN && !M::IS_ODE) {
+          const int k0 = dae_init<M>(u, p, tb, a.t0, a.abstol, LU);
+          init_fail = k0 < 0;
+          nf += k0 < 0 ? -k0 : k0;
+        }
         while (is < a.n_save && a.saveat[is] <= t) {
           if (a.saveat[is] == t) {
 #pragma unroll
@@ -233,6 +243,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
         if (!ROSEN) { M::rhs(u, p, t, tb, k[0]); nf++; }   // k[0] = f(u,t), kept across rejections
         active = true;
         if (!(t < a.t1)) rc = RC_SUCCESS;
+        if (init_fail) rc = RC_INITIALFAILURE;
       }
     }
     // block-wide barrier + vote: keeps the warps of a CTA in step, so the (large) straight-line
@@ -397,6 +408,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
       const double qnan = __longlong_as_double(0x7ff8000000000000LL);
       for (; is < a.n_save; is++)
         for (int i = 0; i < N; i++) a.out_u[((size_t)is * N + i) * a.N + traj] = qnan;
+      mb_retire(a, traj);
       active = false;
     }
   }

@@ -25,6 +25,10 @@
 #define MB_R_BLOCK 256
 #endif
 #define MB_S_STRIDE MB_R_BLOCK
+#if MB_ROWS_SMEM == 4
+#define MB_LU_AT(k) LU[(k) * MB_S_STRIDE]
+#define MB_ROWS_NLU 152
+#endif
 #include "generated/mbm_robot6dof.h"
 #ifndef MB_R_MINB
 #define MB_R_MINB 1

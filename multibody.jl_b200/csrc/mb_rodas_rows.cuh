@@ -39,12 +39,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const u = &W[R_U][0];
   double* const dT = &W[R_DT][0];
   double* const p = &W[R_P][0];
-  double* const LU = &W[R_LU][0];
-  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2;
+  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2, SLU = MB_ROWS_SMEM == 4;   // mode 4: LU slots in shared memory too
   constexpr bool SDT = SROWS && MB_ROWS_SMEM != 3 && M::HAS_DT;            // mode 3: only the C-sum row
   constexpr int S_DT = N, S_US = (SDT ? 2 : 1) * N;     // shared rows: sc | df/dt (if any) | us (mode 2)
 #define MB_US(i) (*(SUS ? &srow[(size_t)(S_US + (i)) * BLOCK] : &us[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
+  double* const LU = SLU ? srow + (size_t)(2 * N) * BLOCK : &W[R_LU][0];   // mode 4: strided by MB_LU_AT (model TU)
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
   long long traj = -1, iter = 0;
   int is = 0, naccept = 0, nreject = 0, nf = 0, njac = 0, nsolve = 0;
@@ -67,7 +67,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         for (int i = 0; i < M::NP; i++) p[i] = a.p[(size_t)i * a.N + traj];
         t = a.t0; is = 0; iter = 0; qold = QOLDINIT;
         naccept = nreject = nf = njac = nsolve = 0;
-        if (!M::IS_ODE) nf += dae_init<M>(u, p, tb, a.t0, a.abstol, LU);
+        bool init_fail = false;
+        if (!M::IS_ODE) {
+          const int k0 = dae_init<M>(u, p, tb, a.t0, a.abstol, LU);
+          init_fail = k0 < 0;
+          nf += k0 < 0 ? -k0 : k0;
+        }
         while (is < a.n_save && a.saveat[is] <= t) {
           if (a.saveat[is] == t) {
 #pragma unroll
@@ -82,6 +87,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         }
         active = true;
         if (!(t < a.t1)) rc = RC_SUCCESS;
+        if (init_fail) rc = RC_INITIALFAILURE;
       }
     }
     if (!__syncthreads_or(active)) break;     // block-lockstep stepping (see mb_ensemble.cuh)
@@ -213,6 +219,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
       const double qnan = __longlong_as_double(0x7ff8000000000000LL);
       for (; is < a.n_save; is++)
         for (int i = 0; i < N; i++) a.out_u[((size_t)is * N + i) * a.N + traj] = qnan;
+      mb_retire(a, traj);
       active = false;
     }
   }

@@ -1,12 +1,25 @@
 // libmultibody_b200 runtime: C ABI (include/mbb200.h), device management, sharding,
-// host<->device staging, ensemble-statistic reduction, FP64 peak probe.
+// host<->device staging (streamed: finished chunks of trajectories are copied back while the
+// ensemble kernel is still running), ensemble-statistic reduction (NCCL across processes),
+// FP64 peak probe.
 // No CPU fallback: every compute entry fails with MBB200_ERR_NO_DEVICE without a GPU.
+//
+// Threading ("re-entrant per model handle"): every entry point takes the
+// registry lock shared (init / shutdown take it exclusively); a solve owns the devices it uses
+// for its duration (per-device mutex, always acquired in device order), so concurrent callers
+// serialise per device instead of racing on the stream, the work counter and the workspace.
+#include <dlfcn.h>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #pragma GCC visibility push(default)
@@ -57,15 +70,22 @@ struct Workspace {          // grow-only device scratch of one device
 struct Device {
   int ordinal = -1;
   int sm_count = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;    // uploads + kernels
+  cudaStream_t cstream = nullptr;   // downloads of finished chunks, concurrent with the kernel
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   unsigned long long* queue = nullptr;
+  unsigned* d_done = nullptr;       // per-chunk count of retired trajectories (device)
+  int* h_flags = nullptr;           // per-chunk "complete" flags: pinned host memory, written by the kernel
+  int* d_flags = nullptr;           // device alias of h_flags
+  int flag_cap = 0;
   Workspace ws;
   double last_ms = 0.0;
   int last_launches = 0;
+  std::mutex mu;                    // held by the call that owns stream / queue / ws
 };
-static std::vector<Device> g_dev;
-static std::mutex g_mu;
+static std::vector<std::unique_ptr<Device>> g_dev;
+static std::shared_mutex g_rw;
+typedef std::shared_lock<std::shared_mutex> RLock;
 
 struct mbb200_model {
   const MbKernelEntry* entry;
@@ -75,13 +95,32 @@ struct mbb200_model {
 
 extern "C" int mbb200_abi_version(void) { return MBB200_ABI_VERSION; }
 extern "C" const char* mbb200_last_error(void) { return g_err; }
-extern "C" int mbb200_device_count(void) { return (int)g_dev.size(); }
+extern "C" int mbb200_device_count(void) {
+  RLock lk(g_rw);
+  return (int)g_dev.size();
+}
+
+static void destroy_device(Device& d) {
+  cudaSetDevice(d.ordinal);
+  if (d.stream) cudaStreamSynchronize(d.stream);
+  if (d.cstream) cudaStreamSynchronize(d.cstream);
+  if (d.ws.ptr) cudaFree(d.ws.ptr);
+  if (d.queue) cudaFree(d.queue);
+  if (d.d_done) cudaFree(d.d_done);
+  if (d.h_flags) cudaFreeHost(d.h_flags);
+  if (d.ev0) cudaEventDestroy(d.ev0);
+  if (d.ev1) cudaEventDestroy(d.ev1);
+  if (d.stream) cudaStreamDestroy(d.stream);
+  if (d.cstream) cudaStreamDestroy(d.cstream);
+}
+
+static void comm_destroy_locked();
 
 extern "C" int mbb200_init_devices(const int* ordinals, int n) {
-  std::lock_guard<std::mutex> lk(g_mu);
+  std::unique_lock<std::shared_mutex> lk(g_rw);
   if (!g_dev.empty()) {
     bool same = (int)g_dev.size() == n;
-    for (int i = 0; same && i < n; i++) same = g_dev[i].ordinal == ordinals[i];
+    for (int i = 0; same && i < n; i++) same = g_dev[i]->ordinal == ordinals[i];
     if (same) return MBB200_OK;
     return fail(MBB200_ERR_BAD_ARG, "already initialised with a different device set; call mbb200_shutdown first");
   }
@@ -89,23 +128,35 @@ extern "C" int mbb200_init_devices(const int* ordinals, int n) {
   cudaError_t e = cudaGetDeviceCount(&count);
   if (e != cudaSuccess || count == 0)
     return fail(MBB200_ERR_NO_DEVICE, "no CUDA device: %s", e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
-  if (n < 1) return fail(MBB200_ERR_BAD_ARG, "n_gpus must be >= 1");
-  std::vector<Device> devs(n);
+  if (n < 1 || !ordinals) return fail(MBB200_ERR_BAD_ARG, "n_gpus must be >= 1");
+  std::vector<std::unique_ptr<Device>> devs;
+  auto bail = [&](int rc) {
+    for (auto& d : devs) destroy_device(*d);
+    return rc;
+  };
   for (int i = 0; i < n; i++) {
     if (ordinals[i] < 0 || ordinals[i] >= count)
-      return fail(MBB200_ERR_NO_DEVICE, "device ordinal %d not present (%d visible)", ordinals[i], count);
-    Device& d = devs[i];
+      return bail(fail(MBB200_ERR_NO_DEVICE, "device ordinal %d not present (%d visible)", ordinals[i], count));
+    devs.emplace_back(new Device);
+    Device& d = *devs.back();
     d.ordinal = ordinals[i];
-    CU(cudaSetDevice(d.ordinal));
     cudaDeviceProp prop;
-    CU(cudaGetDeviceProperties(&prop, d.ordinal));
+    cudaError_t ce = cudaSetDevice(d.ordinal);
+    if (ce == cudaSuccess) ce = cudaGetDeviceProperties(&prop, d.ordinal);
+    if (ce != cudaSuccess) return bail(fail(MBB200_ERR_CUDA, "device %d: %s", d.ordinal, cudaGetErrorString(ce)));
     if (prop.major < 10)
-      return fail(MBB200_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", d.ordinal, prop.major, prop.minor);
+      return bail(fail(MBB200_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", d.ordinal, prop.major, prop.minor));
     d.sm_count = prop.multiProcessorCount;
-    CU(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
-    CU(cudaEventCreate(&d.ev0));
-    CU(cudaEventCreate(&d.ev1));
-    CU(cudaMalloc(&d.queue, sizeof(unsigned long long)));
+    d.flag_cap = 4096;
+    ce = cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaStreamCreateWithFlags(&d.cstream, cudaStreamNonBlocking);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&d.ev0);
+    if (ce == cudaSuccess) ce = cudaEventCreate(&d.ev1);
+    if (ce == cudaSuccess) ce = cudaMalloc(&d.queue, sizeof(unsigned long long));
+    if (ce == cudaSuccess) ce = cudaMalloc(&d.d_done, sizeof(unsigned) * d.flag_cap);
+    if (ce == cudaSuccess) ce = cudaHostAlloc(&d.h_flags, sizeof(int) * d.flag_cap, cudaHostAllocMapped | cudaHostAllocPortable);
+    if (ce == cudaSuccess) ce = cudaHostGetDevicePointer((void**)&d.d_flags, d.h_flags, 0);
+    if (ce != cudaSuccess) return bail(fail(MBB200_ERR_CUDA, "device %d setup: %s", d.ordinal, cudaGetErrorString(ce)));
   }
   g_dev.swap(devs);
   return MBB200_OK;
@@ -119,20 +170,16 @@ extern "C" int mbb200_init(int n_gpus) {
 }
 
 extern "C" void mbb200_shutdown(void) {
-  std::lock_guard<std::mutex> lk(g_mu);
-  for (Device& d : g_dev) {
-    cudaSetDevice(d.ordinal);
-    cudaStreamSynchronize(d.stream);
-    if (d.ws.ptr) cudaFree(d.ws.ptr);
-    if (d.queue) cudaFree(d.queue);
-    cudaEventDestroy(d.ev0);
-    cudaEventDestroy(d.ev1);
-    cudaStreamDestroy(d.stream);
+  std::unique_lock<std::shared_mutex> lk(g_rw);
+  comm_destroy_locked();
+  for (auto& d : g_dev) {
+    std::lock_guard<std::mutex> dl(d->mu);
+    destroy_device(*d);
   }
   g_dev.clear();
 }
 
-static int ws_reserve(Device& d, size_t bytes) {
+static int ws_reserve(Device& d, size_t bytes) {     // caller holds d.mu
   if (d.ws.bytes >= bytes) return MBB200_OK;
   if (d.ws.ptr) CU(cudaFree(d.ws.ptr));
   d.ws.ptr = nullptr;
@@ -145,8 +192,10 @@ static int ws_reserve(Device& d, size_t bytes) {
 // ---------------------------------------------------------------------------------------
 // models
 // ---------------------------------------------------------------------------------------
+static void model_free_locked(mbb200_model* m);
 extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** out) {
   if (!image || !out || len < sizeof(mbb200_image_header)) return fail(MBB200_ERR_BAD_ARG, "bad model image");
+  RLock rl(g_rw);
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
   mbb200_image_header h;
   std::memcpy(&h, image, sizeof(h));
@@ -194,12 +243,12 @@ extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** o
   }
   m->d_tables.assign(g_dev.size(), nullptr);
   for (size_t i = 0; i < g_dev.size(); i++) {
-    cudaError_t ce = cudaSetDevice(g_dev[i].ordinal);
+    cudaError_t ce = cudaSetDevice(g_dev[i]->ordinal);
     if (ce == cudaSuccess) ce = cudaMalloc(&m->d_tables[i], m->tables.size() * sizeof(double));
     if (ce == cudaSuccess) ce = cudaMemcpy(m->d_tables[i], m->tables.data(), m->tables.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (ce != cudaSuccess) {
       int rc = fail(MBB200_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(ce));
-      mbb200_model_free(m);
+      model_free_locked(m);
       return rc;
     }
   }
@@ -207,14 +256,18 @@ extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** o
   return MBB200_OK;
 }
 
-extern "C" void mbb200_model_free(mbb200_model* m) {
+static void model_free_locked(mbb200_model* m) {
   if (!m) return;
   for (size_t i = 0; i < m->d_tables.size() && i < g_dev.size(); i++)
     if (m->d_tables[i]) {
-      cudaSetDevice(g_dev[i].ordinal);
+      cudaSetDevice(g_dev[i]->ordinal);
       cudaFree(m->d_tables[i]);
     }
   delete m;
+}
+extern "C" void mbb200_model_free(mbb200_model* m) {
+  RLock rl(g_rw);
+  model_free_locked(m);
 }
 
 extern "C" int mbb200_model_info(const mbb200_model* m, int32_t* n, int32_t* mm) {
@@ -257,6 +310,137 @@ __global__ void __launch_bounds__(256) mb_reduce_kernel(const double* __restrict
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// cross-process reduction of the ensemble statistic ("one
+// ncclAllReduce(sum, f64) over [count, sum x, sum x^2] ... only when the caller asks for an
+// ensemble statistic").  NCCL is bound at run time (dlopen of libnccl.so.2: the copy already
+// loaded in the process, MBB200_NCCL_LIB, or the system one), so the library itself links
+// only cudart and single-process users need no NCCL at all.
+// ---------------------------------------------------------------------------------------
+namespace {
+struct NcclId { char internal[128]; };
+typedef void* NcclComm;
+struct NcclApi {
+  void* handle = nullptr;
+  int (*GetUniqueId)(NcclId*) = nullptr;
+  int (*CommInitRank)(NcclComm*, int, NcclId, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+  int (*CommDestroy)(NcclComm) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+NcclComm g_comm = nullptr;
+int g_comm_rank = 0, g_comm_size = 1;
+std::mutex g_comm_mu;
+constexpr int kNcclFloat64 = 8, kNcclSum = 0;
+
+int nccl_bind() {
+  if (g_nccl.handle) return MBB200_OK;
+  const char* cands[4] = {getenv("MBB200_NCCL_LIB"), "libnccl.so.2", "libnccl.so", nullptr};
+  void* h = nullptr;
+  for (int i = 0; i < 3 && !h; i++)
+    if (cands[i] && cands[i][0]) h = dlopen(cands[i], RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return fail(MBB200_ERR_UNSUPPORTED, "NCCL not found (set MBB200_NCCL_LIB): %s", dlerror());
+  g_nccl.GetUniqueId = (int (*)(NcclId*))dlsym(h, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(NcclComm*, int, NcclId, int))dlsym(h, "ncclCommInitRank");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, NcclComm, cudaStream_t))dlsym(h, "ncclAllReduce");
+  g_nccl.CommDestroy = (int (*)(NcclComm))dlsym(h, "ncclCommDestroy");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) {
+    dlclose(h);
+    return fail(MBB200_ERR_UNSUPPORTED, "libnccl lacks a required entry point");
+  }
+  g_nccl.handle = h;
+  return MBB200_OK;
+}
+const char* nccl_err(int rc) { return g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error"; }
+}  // namespace
+
+static void comm_destroy_locked() {
+  std::lock_guard<std::mutex> lk(g_comm_mu);
+  if (g_comm) {
+    if (!g_dev.empty()) cudaSetDevice(g_dev[0]->ordinal);
+    g_nccl.CommDestroy(g_comm);
+  }
+  g_comm = nullptr;
+  g_comm_rank = 0;
+  g_comm_size = 1;
+}
+
+extern "C" int mbb200_comm_unique_id(void* id_out, size_t len) {
+  if (!id_out || len < sizeof(NcclId)) return fail(MBB200_ERR_BAD_ARG, "id buffer must hold %d bytes", (int)sizeof(NcclId));
+  std::lock_guard<std::mutex> lk(g_comm_mu);
+  int rc = nccl_bind();
+  if (rc) return rc;
+  NcclId id;
+  int nrc = g_nccl.GetUniqueId(&id);
+  if (nrc != 0) return fail(MBB200_ERR_CUDA, "ncclGetUniqueId: %s", nccl_err(nrc));
+  std::memcpy(id_out, &id, sizeof(id));
+  return MBB200_OK;
+}
+
+extern "C" int mbb200_comm_init(const void* id, size_t len, int rank, int nranks) {
+  RLock rl(g_rw);
+  if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
+  if (!id || len < sizeof(NcclId) || nranks < 1 || rank < 0 || rank >= nranks) return fail(MBB200_ERR_BAD_ARG, "bad communicator arguments");
+  std::lock_guard<std::mutex> lk(g_comm_mu);
+  if (g_comm) return fail(MBB200_ERR_BAD_ARG, "communicator already initialised");
+  int rc = nccl_bind();
+  if (rc) return rc;
+  NcclId nid;
+  std::memcpy(&nid, id, sizeof(nid));
+  CU(cudaSetDevice(g_dev[0]->ordinal));          // one process per GPU: the communicator lives on device 0 of this process
+  NcclComm c = nullptr;
+  int nrc = g_nccl.CommInitRank(&c, nranks, nid, rank);
+  if (nrc != 0) return fail(MBB200_ERR_CUDA, "ncclCommInitRank: %s", nccl_err(nrc));
+  g_comm = c;
+  g_comm_rank = rank;
+  g_comm_size = nranks;
+  return MBB200_OK;
+}
+
+extern "C" int mbb200_comm_info(int* rank, int* nranks) {
+  std::lock_guard<std::mutex> lk(g_comm_mu);
+  if (rank) *rank = g_comm_rank;
+  if (nranks) *nranks = g_comm_size;
+  return g_comm ? 1 : 0;
+}
+
+// sum over ranks, in place, device buffer on device 0, ordered after everything already on `st`
+static int comm_allreduce_dev(Device& d, double* d_buf, size_t count, cudaStream_t st) {
+  std::lock_guard<std::mutex> lk(g_comm_mu);
+  if (!g_comm || count == 0) return MBB200_OK;
+  int nrc = g_nccl.AllReduce(d_buf, d_buf, count, kNcclFloat64, kNcclSum, g_comm, st);
+  if (nrc != 0) return fail(MBB200_ERR_CUDA, "ncclAllReduce: %s", nccl_err(nrc));
+  return MBB200_OK;
+}
+
+extern "C" int mbb200_comm_allreduce(double* host_buf, int64_t count) {
+  RLock rl(g_rw);
+  if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
+  if (!host_buf || count < 0) return fail(MBB200_ERR_BAD_ARG, "bad buffer");
+  {
+    std::lock_guard<std::mutex> lk(g_comm_mu);
+    if (!g_comm) return MBB200_OK;                // single process: the local sum is the global sum
+  }
+  Device& d = *g_dev[0];
+  std::lock_guard<std::mutex> dl(d.mu);
+  CU(cudaSetDevice(d.ordinal));
+  int rc = ws_reserve(d, sizeof(double) * (size_t)count);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(d.ws.ptr, host_buf, sizeof(double) * count, cudaMemcpyHostToDevice, d.stream));
+  rc = comm_allreduce_dev(d, (double*)d.ws.ptr, (size_t)count, d.stream);
+  if (rc) return rc;
+  CU(cudaMemcpyAsync(host_buf, d.ws.ptr, sizeof(double) * count, cudaMemcpyDeviceToHost, d.stream));
+  CU(cudaStreamSynchronize(d.stream));
+  return MBB200_OK;
+}
+
+extern "C" void mbb200_comm_destroy(void) {
+  RLock rl(g_rw);
+  comm_destroy_locked();
+}
+
 static int check_opts(const mbb200_model* m, const mbb200_opts* o, long long N, int n_save) {
   if (!m || !o) return fail(MBB200_ERR_BAD_ARG, "null model or options");
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
@@ -271,10 +455,18 @@ static int check_opts(const mbb200_model* m, const mbb200_opts* o, long long N, 
   return MBB200_OK;
 }
 
-// enqueue one shard on device d (everything already resident); timing events around the kernels
+// trajectories per completion chunk: a power of two, at least 8192, at most flag_cap chunks per shard
+static int chunk_shift_for(const Device& d, long long Ns) {
+  int sh = 13;
+  while (((Ns + (1ll << sh) - 1) >> sh) > d.flag_cap) sh++;
+  return sh;
+}
+
+// enqueue one shard on device d (everything already resident); timing events around the kernels.
+// `stream_chunks`: the kernel reports finished chunks of 2^chunk_shift trajectories through d.h_flags.
 static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const mbb200_opts* o, long long Ns,
                          const double* d_u0, const double* d_p, const double* d_saveat, int n_save, double* d_out_u,
-                         double* d_tfinal, int* d_rc, int* d_stats, double* d_reduce) {
+                         double* d_tfinal, int* d_rc, int* d_stats, double* d_reduce, bool stream_chunks, int chunk_shift) {
   MbArgs a;
   a.N = Ns; a.u0 = d_u0; a.p = d_p; a.tb = m->d_tables[dev_index]; a.saveat = d_saveat; a.n_save = n_save;
   a.out_u = d_out_u; a.out_tfinal = d_tfinal; a.retcode = d_rc; a.stats = d_stats; a.queue = d.queue;
@@ -282,8 +474,15 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
   a.dtmax = o->dtmax; a.maxiters = o->maxiters;
   a.qs_min = o->qsteady_min; a.qs_max = o->qsteady_max; a.pow_mode = o->pow_mode;
   if (a.qs_min == 0.0 && a.qs_max == 0.0) { a.qs_min = 1.0; a.qs_max = (o->alg == MBB200_ALG_TSIT5) ? 1.0 : 1.2; }
+  a.done = nullptr; a.flags = nullptr; a.chunk_shift = 0;
   d.last_launches = 0;
   CU(cudaMemsetAsync(d.queue, 0, sizeof(unsigned long long), d.stream));
+  if (stream_chunks && Ns > 0) {
+    const long long nch = (Ns + (1ll << chunk_shift) - 1) >> chunk_shift;
+    CU(cudaMemsetAsync(d.d_done, 0, sizeof(unsigned) * (size_t)nch, d.stream));
+    for (long long c = 0; c < nch; c++) d.h_flags[c] = 0;
+    a.done = d.d_done; a.flags = d.d_flags; a.chunk_shift = chunk_shift;
+  }
   CU(cudaEventRecord(d.ev0, d.stream));
   if (Ns > 0) {
     cudaError_t e = m->entry->launch(o->alg, a, d.sm_count, d.stream);
@@ -303,6 +502,7 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
 static int finish_shard(Device& d) {
   CU(cudaSetDevice(d.ordinal));
   CU(cudaStreamSynchronize(d.stream));
+  CU(cudaStreamSynchronize(d.cstream));
   float ms = 0.f;
   CU(cudaEventElapsedTime(&ms, d.ev0, d.ev1));
   d.last_ms = ms;
@@ -312,24 +512,48 @@ static int finish_shard(Device& d) {
 extern "C" int mbb200_solve_device(mbb200_model* m, const mbb200_opts* o, int dev_index, int64_t N, const double* d_u0,
                                    const double* d_p, const double* saveat, int32_t n_save, double* d_out_u,
                                    double* d_tfinal, int32_t* d_rc, int32_t* d_stats, double* d_reduce) {
+  RLock rl(g_rw);
   int rc = check_opts(m, o, N, n_save);
   if (rc) return rc;
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index %d", dev_index);
   if (!d_u0 || !d_tfinal || !d_rc || !d_stats || (n_save > 0 && (!saveat || !d_out_u)) || (m->entry->m > 0 && !d_p))
     return fail(MBB200_ERR_BAD_ARG, "null buffer");
-  Device& d = g_dev[dev_index];
+  Device& d = *g_dev[dev_index];
+  std::lock_guard<std::mutex> dl(d.mu);
   CU(cudaSetDevice(d.ordinal));
   rc = ws_reserve(d, sizeof(double) * (size_t)(n_save > 0 ? n_save : 1));
   if (rc) return rc;
   if (n_save > 0) CU(cudaMemcpyAsync(d.ws.ptr, saveat, sizeof(double) * n_save, cudaMemcpyHostToDevice, d.stream));
-  rc = enqueue_shard(d, m, dev_index, o, N, d_u0, d_p, (const double*)d.ws.ptr, n_save, d_out_u, d_tfinal, d_rc, d_stats, d_reduce);
-  if (rc) return rc;
-  return finish_shard(d);
+  rc = enqueue_shard(d, m, dev_index, o, N, d_u0, d_p, (const double*)d.ws.ptr, n_save, d_out_u, d_tfinal, d_rc, d_stats,
+                     d_reduce, false, 0);
+  if (rc == MBB200_OK && (o->flags & MBB200_FLAG_REDUCE) && d_reduce && n_save > 0 && dev_index == 0) {
+    if (N == 0) CU(cudaMemsetAsync(d_reduce, 0, sizeof(double) * (2 * (size_t)n_save * m->entry->n + 1), d.stream));
+    rc = comm_allreduce_dev(d, d_reduce, 2 * (size_t)n_save * m->entry->n + 1, d.stream);   // no-op without a communicator
+  }
+  int rc2 = finish_shard(d);     // always drain what was enqueued before returning
+  return rc ? rc : rc2;
 }
+
+// Page-locks a caller buffer for the duration of a call when it is ordinary pageable memory
+// (what a Julia `Array` is): copies from pageable memory are staged by the driver and are
+// neither asynchronous nor fast.  Failure to register is not an error (the copy still works).
+struct HostPin {
+  void* p = nullptr;
+  void pin(const void* ptr, size_t bytes) {
+    if (!ptr || bytes < (size_t(1) << 20) || getenv("MBB200_NO_HOST_REGISTER")) return;
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return; }
+    if (at.type != cudaMemoryTypeUnregistered) return;
+    if (cudaHostRegister(const_cast<void*>(ptr), bytes, cudaHostRegisterPortable) == cudaSuccess) p = const_cast<void*>(ptr);
+    else cudaGetLastError();
+  }
+  ~HostPin() { if (p) cudaHostUnregister(p); }
+};
 
 extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, const double* u0, const double* p,
                             const double* saveat, int32_t n_save, double* out_u, double* out_tfinal, int32_t* retcode,
                             int32_t* stats, double* reduce_out) {
+  RLock rl(g_rw);
   int rc = check_opts(m, o, N, n_save);
   if (rc) return rc;
   const int n = m->entry->n, mp = m->entry->m;
@@ -338,19 +562,48 @@ extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, co
   const int G = (int)g_dev.size();
   const bool want_red = (o->flags & MBB200_FLAG_REDUCE) && reduce_out && n_save > 0;
   const int rows = n_save * n;
-  struct Shard { long long off, Ns; double *u0, *p, *sv, *out, *tf, *red; int *rc, *st; };
+  std::vector<std::unique_lock<std::mutex>> own;          // devices are owned in index order: no lock cycles
+  for (int g = 0; g < G; g++) own.emplace_back(g_dev[g]->mu);
+  HostPin pins[6];
+  pins[0].pin(u0, sizeof(double) * (size_t)N * n);
+  pins[1].pin(p, sizeof(double) * (size_t)N * mp);
+  pins[2].pin(out_u, sizeof(double) * (size_t)N * rows);
+  pins[3].pin(out_tfinal, sizeof(double) * (size_t)N);
+  pins[4].pin(retcode, sizeof(int) * (size_t)N);
+  pins[5].pin(stats, sizeof(int) * (size_t)N * 5);
+  struct Shard { long long off = 0, Ns = 0, nch = 0, next = 0; int shift = 0; bool started = false;
+                 double *u0 = 0, *p = 0, *sv = 0, *out = 0, *tf = 0, *red = 0; int *rc = 0, *st = 0; };
   std::vector<Shard> sh(G);
+  // on any failure: drain every stream that has work of this call in flight, then report
+  auto drain = [&](int code) {
+    for (int g = 0; g < G; g++)
+      if (sh[g].started) {
+        cudaSetDevice(g_dev[g]->ordinal);
+        cudaStreamSynchronize(g_dev[g]->stream);
+        cudaStreamSynchronize(g_dev[g]->cstream);
+      }
+    return code;
+  };
+#define CUD(call)                                                                                         \
+  do {                                                                                                    \
+    cudaError_t e_ = (call);                                                                              \
+    if (e_ != cudaSuccess)                                                                                \
+      return drain(fail(MBB200_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__)); \
+  } while (0)
   for (int g = 0; g < G; g++) {
-    Device& d = g_dev[g];
+    Device& d = *g_dev[g];
     Shard& s = sh[g];
     s.off = N * g / G;
     s.Ns = N * (g + 1) / G - s.off;
-    CU(cudaSetDevice(d.ordinal));
+    d.last_ms = 0.0;
+    d.last_launches = 0;
+    if (s.Ns == 0) continue;                               // nothing to do on this device (N < number of devices)
+    CUD(cudaSetDevice(d.ordinal));
     const size_t Np = ((size_t)s.Ns + 31) & ~(size_t)31;    // keep every sub-array 256-byte aligned
     size_t nd = Np * (size_t)(n + mp + rows + 1) + (size_t)((n_save + 31) & ~31) + (size_t)(2 * rows + 1 + 31);
     size_t bytes = nd * sizeof(double) + Np * 6 * sizeof(int) + 1024;
     rc = ws_reserve(d, bytes);
-    if (rc) return rc;
+    if (rc) return drain(rc);
     double* w = (double*)d.ws.ptr;
     s.u0 = w; w += Np * n;
     s.p = w; w += Np * mp;
@@ -360,28 +613,81 @@ extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, co
     s.red = w; w += (2 * rows + 1 + 31) & ~31;
     s.rc = (int*)w;
     s.st = s.rc + Np;
-    if (s.Ns == 0) continue;
+    s.shift = chunk_shift_for(d, s.Ns);
+    s.nch = (s.Ns + (1ll << s.shift) - 1) >> s.shift;
+    s.started = true;
     const size_t wb = (size_t)s.Ns * sizeof(double);
-    CU(cudaMemcpy2DAsync(s.u0, wb, u0 + s.off, (size_t)N * sizeof(double), wb, n, cudaMemcpyHostToDevice, d.stream));
-    if (mp > 0) CU(cudaMemcpy2DAsync(s.p, wb, p + s.off, (size_t)N * sizeof(double), wb, mp, cudaMemcpyHostToDevice, d.stream));
-    if (n_save > 0) CU(cudaMemcpyAsync(s.sv, saveat, sizeof(double) * n_save, cudaMemcpyHostToDevice, d.stream));
-    rc = enqueue_shard(d, m, g, o, s.Ns, s.u0, s.p, s.sv, n_save, s.out, s.tf, s.rc, s.st, want_red ? s.red : nullptr);
-    if (rc) return rc;
-    if (n_save > 0)
-      CU(cudaMemcpy2DAsync(out_u + s.off, (size_t)N * sizeof(double), s.out, wb, wb, rows, cudaMemcpyDeviceToHost, d.stream));
-    CU(cudaMemcpyAsync(out_tfinal + s.off, s.tf, wb, cudaMemcpyDeviceToHost, d.stream));
-    CU(cudaMemcpyAsync(retcode + s.off, s.rc, (size_t)s.Ns * sizeof(int), cudaMemcpyDeviceToHost, d.stream));
-    CU(cudaMemcpy2DAsync(stats + s.off, (size_t)N * sizeof(int), s.st, (size_t)s.Ns * sizeof(int), (size_t)s.Ns * sizeof(int), 5,
-                         cudaMemcpyDeviceToHost, d.stream));
+    CUD(cudaMemcpy2DAsync(s.u0, wb, u0 + s.off, (size_t)N * sizeof(double), wb, n, cudaMemcpyHostToDevice, d.stream));
+    if (mp > 0) CUD(cudaMemcpy2DAsync(s.p, wb, p + s.off, (size_t)N * sizeof(double), wb, mp, cudaMemcpyHostToDevice, d.stream));
+    if (n_save > 0) CUD(cudaMemcpyAsync(s.sv, saveat, sizeof(double) * n_save, cudaMemcpyHostToDevice, d.stream));
+    rc = enqueue_shard(d, m, g, o, s.Ns, s.u0, s.p, s.sv, n_save, s.out, s.tf, s.rc, s.st, want_red ? s.red : nullptr, true, s.shift);
+    if (rc) return drain(rc);
   }
+  // Streamed read-back: a chunk of trajectories is copied to the caller's buffers as soon as the
+  // kernel has retired all of it (per-chunk counters, flag in mapped host memory), on the copy
+  // stream, while the kernel keeps integrating the rest.  When the kernel has finished, whatever
+  // is left is copied at once.
+  int pending = 0;
+  for (int g = 0; g < G; g++) pending += sh[g].started ? 1 : 0;
+  while (pending > 0) {
+    bool progressed = false;
+    for (int g = 0; g < G; g++) {
+      Shard& s = sh[g];
+      if (!s.started || s.next >= s.nch) continue;
+      Device& d = *g_dev[g];
+      long long c1 = s.next;
+      while (c1 < s.nch && *(volatile int*)&d.h_flags[c1]) c1++;
+      if (c1 == s.next) {
+        cudaError_t q = cudaEventQuery(d.ev1);
+        if (q == cudaSuccess) c1 = s.nch;                  // kernel done: everything is ready
+        else if (q != cudaErrorNotReady) return drain(fail(MBB200_ERR_CUDA, "ensemble kernel failed: %s", cudaGetErrorString(q)));
+        else continue;
+      }
+      CUD(cudaSetDevice(d.ordinal));
+      const long long a0 = s.next << s.shift;
+      long long a1 = c1 << s.shift;
+      if (a1 > s.Ns) a1 = s.Ns;
+      const size_t cw = (size_t)(a1 - a0) * sizeof(double), ci = (size_t)(a1 - a0) * sizeof(int);
+      const size_t wb = (size_t)s.Ns * sizeof(double), wi = (size_t)s.Ns * sizeof(int);
+      if (n_save > 0)
+        CUD(cudaMemcpy2DAsync(out_u + s.off + a0, (size_t)N * sizeof(double), s.out + a0, wb, cw, rows, cudaMemcpyDeviceToHost, d.cstream));
+      CUD(cudaMemcpyAsync(out_tfinal + s.off + a0, s.tf + a0, cw, cudaMemcpyDeviceToHost, d.cstream));
+      CUD(cudaMemcpyAsync(retcode + s.off + a0, s.rc + a0, ci, cudaMemcpyDeviceToHost, d.cstream));
+      CUD(cudaMemcpy2DAsync(stats + s.off + a0, (size_t)N * sizeof(int), s.st + a0, wi, ci, 5, cudaMemcpyDeviceToHost, d.cstream));
+      s.next = c1;
+      progressed = true;
+      if (s.next >= s.nch) pending--;
+    }
+    if (!progressed) std::this_thread::sleep_for(std::chrono::microseconds(50));
+  }
+#undef CUD
   if (want_red) std::memset(reduce_out, 0, sizeof(double) * (2 * rows + 1));
   std::vector<double> part(want_red ? 2 * rows + 1 : 0);
+  int first_err = MBB200_OK;
   for (int g = 0; g < G; g++) {
-    rc = finish_shard(g_dev[g]);
-    if (rc) return rc;
-    if (want_red && sh[g].Ns > 0) {
-      CU(cudaMemcpy(part.data(), sh[g].red, sizeof(double) * part.size(), cudaMemcpyDeviceToHost));
+    if (!sh[g].started) continue;
+    rc = finish_shard(*g_dev[g]);
+    if (rc) { if (!first_err) first_err = rc; continue; }
+    if (want_red && !first_err) {
+      cudaError_t ce = cudaMemcpy(part.data(), sh[g].red, sizeof(double) * part.size(), cudaMemcpyDeviceToHost);
+      if (ce != cudaSuccess) { first_err = fail(MBB200_ERR_CUDA, "statistics read-back failed: %s", cudaGetErrorString(ce)); continue; }
       for (size_t i = 0; i < part.size(); i++) reduce_out[i] += part[i];
+    }
+  }
+  if (first_err) return first_err;
+  if (want_red) {
+    bool have_comm;
+    { std::lock_guard<std::mutex> lk(g_comm_mu); have_comm = g_comm != nullptr; }
+    if (have_comm) {                                       // sum over the processes of the job (NCCL)
+      Device& d = *g_dev[0];
+      CU(cudaSetDevice(d.ordinal));
+      rc = ws_reserve(d, sizeof(double) * part.size());
+      if (rc) return rc;
+      CU(cudaMemcpyAsync(d.ws.ptr, reduce_out, sizeof(double) * part.size(), cudaMemcpyHostToDevice, d.stream));
+      rc = comm_allreduce_dev(d, (double*)d.ws.ptr, part.size(), d.stream);
+      if (rc) { cudaStreamSynchronize(d.stream); return rc; }
+      CU(cudaMemcpyAsync(reduce_out, d.ws.ptr, sizeof(double) * part.size(), cudaMemcpyDeviceToHost, d.stream));
+      CU(cudaStreamSynchronize(d.stream));
     }
   }
   return MBB200_OK;
@@ -397,6 +703,7 @@ extern "C" int mbb200_model_observed_count(const mbb200_model* m, int32_t* nobs)
 
 extern "C" int mbb200_observed(mbb200_model* m, int64_t N, const double* u, const double* p, const double* saveat,
                                int32_t n_save, double* out_obs) {
+  RLock rl(g_rw);
   if (!m) return fail(MBB200_ERR_BAD_ARG, "null model");
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
   const int n = m->entry->n, mp = m->entry->m, nobs = m->entry->nobs;
@@ -404,7 +711,8 @@ extern "C" int mbb200_observed(mbb200_model* m, int64_t N, const double* u, cons
   if (N < 0 || n_save < 0) return fail(MBB200_ERR_BAD_ARG, "negative size");
   if (N == 0 || n_save == 0) return MBB200_OK;
   if (!u || !saveat || !out_obs || (mp > 0 && !p)) return fail(MBB200_ERR_BAD_ARG, "null buffer");
-  Device& d = g_dev[0];
+  Device& d = *g_dev[0];
+  std::lock_guard<std::mutex> dl(d.mu);
   CU(cudaSetDevice(d.ordinal));
   // processed in slabs of save points so the workspace stays bounded
   const size_t per_save = (size_t)N * (n + nobs) * sizeof(double);
@@ -436,9 +744,10 @@ extern "C" int mbb200_observed(mbb200_model* m, int64_t N, const double* u, cons
 }
 
 extern "C" int mbb200_last_timing(int dev_index, double* kernel_ms, int32_t* n_launches) {
+  RLock rl(g_rw);
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index %d", dev_index);
-  if (kernel_ms) *kernel_ms = g_dev[dev_index].last_ms;
-  if (n_launches) *n_launches = g_dev[dev_index].last_launches;
+  if (kernel_ms) *kernel_ms = g_dev[dev_index]->last_ms;
+  if (n_launches) *n_launches = g_dev[dev_index]->last_launches;
   return MBB200_OK;
 }
 
@@ -456,9 +765,11 @@ __global__ void __launch_bounds__(256) mb_dfma_probe(double* out, int iters, dou
 }
 
 extern "C" int mbb200_measure_fp64_peak(int dev_index, double* flops_per_s) {
+  RLock rl(g_rw);
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index %d", dev_index);
   if (!flops_per_s) return fail(MBB200_ERR_BAD_ARG, "null output");
-  Device& d = g_dev[dev_index];
+  Device& d = *g_dev[dev_index];
+  std::lock_guard<std::mutex> dl(d.mu);
   CU(cudaSetDevice(d.ordinal));
   const int blocks = d.sm_count * 8, threads = 256, iters = 1 << 15;
   int rc = ws_reserve(d, sizeof(double) * (size_t)blocks * threads);
@@ -483,30 +794,35 @@ extern "C" int mbb200_measure_fp64_peak(int dev_index, double* flops_per_s) {
 // memory helpers
 // ---------------------------------------------------------------------------------------
 extern "C" int mbb200_dev_alloc(int dev_index, size_t bytes, void** out) {
+  RLock rl(g_rw);
   if (dev_index < 0 || dev_index >= (int)g_dev.size() || !out) return fail(MBB200_ERR_BAD_ARG, "bad argument");
-  CU(cudaSetDevice(g_dev[dev_index].ordinal));
+  CU(cudaSetDevice(g_dev[dev_index]->ordinal));
   CU(cudaMalloc(out, bytes ? bytes : 1));
   return MBB200_OK;
 }
 extern "C" int mbb200_dev_free(int dev_index, void* ptr) {
+  RLock rl(g_rw);
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index");
-  CU(cudaSetDevice(g_dev[dev_index].ordinal));
+  CU(cudaSetDevice(g_dev[dev_index]->ordinal));
   CU(cudaFree(ptr));
   return MBB200_OK;
 }
 extern "C" int mbb200_dev_upload(int dev_index, void* dst, const void* src, size_t bytes) {
+  RLock rl(g_rw);
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index");
-  CU(cudaSetDevice(g_dev[dev_index].ordinal));
+  CU(cudaSetDevice(g_dev[dev_index]->ordinal));
   CU(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
   return MBB200_OK;
 }
 extern "C" int mbb200_dev_download(int dev_index, void* dst, const void* src, size_t bytes) {
+  RLock rl(g_rw);
   if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index");
-  CU(cudaSetDevice(g_dev[dev_index].ordinal));
+  CU(cudaSetDevice(g_dev[dev_index]->ordinal));
   CU(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
   return MBB200_OK;
 }
 extern "C" int mbb200_host_alloc_pinned(size_t bytes, void** out) {
+  RLock rl(g_rw);
   if (!out) return fail(MBB200_ERR_BAD_ARG, "null output");
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
   CU(cudaMallocHost(out, bytes ? bytes : 1));

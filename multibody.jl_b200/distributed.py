@@ -3,13 +3,19 @@
 Trajectory i depends only on (u0_i, p_i) and the shared read-only tables, so ranks never
 exchange trajectory data.  The single collective is the all-reduce of
 the ensemble statistic `[count, sum(x), sum(x^2)]` (SciML `reduction` / `u_init` of an
-EnsembleProblem): 2 * n_save * n + 1 doubles, NCCL over NVLink on GPUs, gloo in CPU tests.
+EnsembleProblem): 2 * n_save * n + 1 doubles.  It runs INSIDE the library
+(`mbb200_comm_init` + `ncclAllReduce` on the solve stream, csrc/mb_runtime.cu); this module only
+distributes the communicator id.  No PyTorch here: the launcher hands in a `broadcast` callable
+(bench.py passes one built on its torchrun rendezvous, a Julia host would use MPI.jl).
 """
 from __future__ import annotations
 
-from typing import Dict, Tuple
+import ctypes as C
+from typing import Callable, Dict, Optional, Tuple
 
 import numpy as np
+
+NCCL_ID_BYTES = 128
 
 
 def shard_range(n_total: int, rank: int, world: int) -> Tuple[int, int]:
@@ -18,21 +24,33 @@ def shard_range(n_total: int, rank: int, world: int) -> Tuple[int, int]:
     return n_total * rank // world, n_total * (rank + 1) // world
 
 
-def allreduce_statistics(red, group=None):
-    """In-place sum over ranks of the raw statistic vector (torch tensor on the rank's device,
-    or a numpy array that is staged through a CPU tensor)."""
-    import torch
-    import torch.distributed as dist
-    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
-        return red
-    if isinstance(red, np.ndarray):
-        t = torch.from_numpy(red)
-        if dist.get_backend(group) == "nccl":
-            t = t.cuda()
-        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
-        red[:] = t.cpu().numpy()
-        return red
-    dist.all_reduce(red, op=dist.ReduceOp.SUM, group=group)
+def comm_init(rank: int, world: int, broadcast: Callable[[Optional[bytes]], bytes]) -> None:
+    """Create the library's NCCL communicator over `world` processes (call after the devices are
+    initialised).  `broadcast(payload_or_None) -> bytes` must return rank 0's payload on every
+    rank (rank 0 passes the id, the others None)."""
+    from . import _lib
+    L = _lib.lib()
+    buf = C.create_string_buffer(NCCL_ID_BYTES)
+    if rank == 0:
+        _lib.check(L.mbb200_comm_unique_id(buf, NCCL_ID_BYTES))
+        ident = broadcast(bytes(buf.raw))
+    else:
+        ident = broadcast(None)
+    if len(ident) != NCCL_ID_BYTES:
+        raise ValueError("communicator id must be 128 bytes")
+    _lib.check(L.mbb200_comm_init(C.create_string_buffer(ident, NCCL_ID_BYTES), NCCL_ID_BYTES, rank, world))
+
+
+def comm_active() -> bool:
+    from . import _lib
+    return bool(_lib.lib().mbb200_comm_info(None, None))
+
+
+def allreduce_statistics(red: np.ndarray) -> np.ndarray:
+    """In-place sum over the ranks of the library communicator (no-op in a single process)."""
+    from . import _lib
+    red = np.ascontiguousarray(red, dtype=np.float64)
+    _lib.check(_lib.lib().mbb200_comm_allreduce(_lib.ptr(red), red.size))
     return red
 
 

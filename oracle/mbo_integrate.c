@@ -27,7 +27,7 @@
 #include "mbo.h"
 
 /* SciMLBase.ReturnCode values */
-enum { RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6 };
+enum { RC_SUCCESS = 1, RC_DTNAN = 3, RC_MAXITERS = 4, RC_DTLESSTHANMIN = 5, RC_UNSTABLE = 6, RC_INITIALFAILURE = 7 };
 
 /* Rosenbrock tableau in the transformed (Hairer-Wanner) form, padded to 8 stages */
 typedef struct {
@@ -83,7 +83,9 @@ static float fastlog2f(float x) {
 static double fastpower(double x, double y) {
   if (x == 0.0) return 0.0;
   if (isinf(x) && isinf(y)) return INFINITY;
-  return (double)exp2f((float)y * fastlog2f((float)x));
+  /* exp2 evaluated in double and rounded to Float32: the same bits on the CPU and on the GPU
+   * (libm's and CUDA's exp2f differ by an ulp, which would flip dead-band decisions) */
+  return (double)(float)exp2((double)((float)y * fastlog2f((float)x)));
 }
 static double ctl_pow(const mbo_opts* o, double x, double y) { return o->pow_mode == 1 ? pow(x, y) : fastpower(x, y); }
 
@@ -227,16 +229,19 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
    * test/test_fourbar.jl:44,70): differential states are kept, the algebraic equations
    * 0 = f_alg(u) are solved by Newton for the algebraic states.  One Newton step is a solve
    * with W = c M - J at c = 1e20, which pins the differential rows. */
+  int init_fail = 0;
   {
     int is_dae = 0;
     for (int i = 0; i < n; i++) if (!mass[i]) is_dae = 1;
     if (is_dae && rosen) {
       const double tol_init = fmin(o->abstol, 1e-10);
-      for (int it = 0; it < 10; it++) {
+      init_fail = 1;
+      for (int it = 0; it <= 10; it++) {
         f_eval(&c, u, t0, du);
         double r = 0.0;
         for (int i = 0; i < n; i++) if (!mass[i]) r = fmax(r, fabs(du[i]));
-        if (!(r > tol_init)) break;
+        if (!(r > tol_init)) { init_fail = 0; break; }
+        if (it == 10) break;
         jac_dense(&c, u, t0, du, 0, J, w1, w2, Jnz);
         c.njac--;
         for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) W[i * n + j] = -J[i * n + j] + ((i == j && mass[i]) ? 1e20 : 0.0);
@@ -259,7 +264,8 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
   int have_fsal = 0;
   const int trace = getenv("MBO_TRACE") != NULL;
 
-  while (t < t1) {
+  if (init_fail) rc = RC_INITIALFAILURE;          /* inconsistent algebraic states: do not integrate */
+  while (t < t1 && !init_fail) {
     if (++iter > maxiters) { rc = RC_MAXITERS; break; }
     if (!isfinite(dt)) { rc = RC_DTNAN; break; }
     if (dt < fmax(o->dtmin, 16.0 * DBL_EPSILON * fmax(fabs(t), 1e-300))) { rc = RC_DTLESSTHANMIN; break; }

@@ -25,7 +25,8 @@ def _worker(rank, world, port, N, q):
     import torch.distributed as dist
     import mbo
     from multibody_jl_b200 import ensembles
-    from multibody_jl_b200.distributed import allreduce_statistics, host_statistics, shard_range
+    import torch
+    from multibody_jl_b200.distributed import host_statistics, shard_range
     from multibody_jl_b200.mechanics.zoo import get_model
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -34,7 +35,10 @@ def _worker(rank, world, port, N, q):
     r = mbo.solve(spec.model, spec.alg, spec.u0, spec.p, get_model(spec.model).tables.pack(), spec.tspan,
                   spec.saveat[:5], abstol=1e-8, reltol=1e-8)
     red = host_statistics(r["u"], r["retcode"])
-    allreduce_statistics(red)
+    # the product sums the statistic inside the library (ncclAllReduce behind mbb200_comm_init, GPU test
+    # test_library_communicator_*); here gloo plays that part so the sharding logic runs on CPU
+    t = torch.from_numpy(red)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
     if rank == 0:
         q.put((lo, hi, red))
     dist.barrier()
