@@ -539,15 +539,30 @@ extern "C" int mbb200_solve_device(mbb200_model* m, const mbb200_opts* o, int de
 // neither asynchronous nor fast.  Failure to register is not an error (the copy still works).
 struct HostPin {
   void* p = nullptr;
-  void pin(const void* ptr, size_t bytes) {
-    if (!ptr || bytes < (size_t(1) << 20) || getenv("MBB200_NO_HOST_REGISTER")) return;
+  std::thread th;
+  static bool wanted(const void* ptr, size_t bytes) {
+    if (!ptr || bytes < (size_t(1) << 20) || getenv("MBB200_NO_HOST_REGISTER")) return false;
     cudaPointerAttributes at;
-    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return; }
-    if (at.type != cudaMemoryTypeUnregistered) return;
+    if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeUnregistered;
+  }
+  void pin(const void* ptr, size_t bytes) {                 // synchronous (inputs: needed before the first copy)
+    if (!wanted(ptr, bytes)) return;
     if (cudaHostRegister(const_cast<void*>(ptr), bytes, cudaHostRegisterPortable) == cudaSuccess) p = const_cast<void*>(ptr);
     else cudaGetLastError();
   }
-  ~HostPin() { if (p) cudaHostUnregister(p); }
+  // outputs: page-locking (which also faults the pages in) runs on a helper thread while the kernel
+  // integrates; wait() is called before the first chunk is copied back
+  void pin_async(const void* ptr, size_t bytes, int ordinal) {
+    if (!wanted(ptr, bytes)) return;
+    th = std::thread([this, ptr, bytes, ordinal]() {
+      cudaSetDevice(ordinal);
+      if (cudaHostRegister(const_cast<void*>(ptr), bytes, cudaHostRegisterPortable) == cudaSuccess) p = const_cast<void*>(ptr);
+      else cudaGetLastError();
+    });
+  }
+  void wait() { if (th.joinable()) th.join(); }
+  ~HostPin() { wait(); if (p) cudaHostUnregister(p); }
 };
 
 extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, const double* u0, const double* p,
@@ -567,10 +582,7 @@ extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, co
   HostPin pins[6];
   pins[0].pin(u0, sizeof(double) * (size_t)N * n);
   pins[1].pin(p, sizeof(double) * (size_t)N * mp);
-  pins[2].pin(out_u, sizeof(double) * (size_t)N * rows);
-  pins[3].pin(out_tfinal, sizeof(double) * (size_t)N);
-  pins[4].pin(retcode, sizeof(int) * (size_t)N);
-  pins[5].pin(stats, sizeof(int) * (size_t)N * 5);
+  const int ord0 = g_dev[0]->ordinal;
   struct Shard { long long off = 0, Ns = 0, nch = 0, next = 0; int shift = 0; bool started = false;
                  double *u0 = 0, *p = 0, *sv = 0, *out = 0, *tf = 0, *red = 0; int *rc = 0, *st = 0; };
   std::vector<Shard> sh(G);
@@ -627,6 +639,11 @@ extern "C" int mbb200_solve(mbb200_model* m, const mbb200_opts* o, int64_t N, co
   // kernel has retired all of it (per-chunk counters, flag in mapped host memory), on the copy
   // stream, while the kernel keeps integrating the rest.  When the kernel has finished, whatever
   // is left is copied at once.
+  pins[2].pin_async(out_u, sizeof(double) * (size_t)N * rows, ord0);      // overlaps the kernels just enqueued
+  pins[3].pin(out_tfinal, sizeof(double) * (size_t)N);
+  pins[4].pin(retcode, sizeof(int) * (size_t)N);
+  pins[5].pin(stats, sizeof(int) * (size_t)N * 5);
+  pins[2].wait();
   int pending = 0;
   for (int g = 0; g < G; g++) pending += sh[g].started ? 1 : 0;
   while (pending > 0) {
