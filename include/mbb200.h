@@ -120,6 +120,23 @@ int mbb200_solve_device(mbb200_model* model, const mbb200_opts* opts, int dev_in
                         double* d_out_u, double* d_out_tfinal, int32_t* d_retcode, int32_t* d_stats,
                         double* d_reduce_out);
 
+/* Allocation-free variant of mbb200_solve_device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Same arguments, layouts and results as
+ * mbb200_solve_device; the kernel's scratch memory (trajectory work counter + device copy of
+ * `saveat`) lives in a static device array of 256 + 8 * MBB200_STATIC_MAX_SAVE bytes that every GPU
+ * loading the library holds until exit, so the call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  Limits and caveats: n_save <= MBB200_STATIC_MAX_SAVE (larger values
+ * are rejected with MBB200_ERR_BAD_ARG); with MBB200_FLAG_REDUCE the statistic is that of this
+ * device only (no cross-process sum); all calls on one GPU share the array, which keeps the last
+ * call's contents (the counter is cleared at the start of every call) -- calls that overlap on the
+ * same GPU would race on it (this library serialises its own calls per device). */
+#define MBB200_STATIC_MAX_SAVE 4096
+int mbb200_solve_device_static(mbb200_model* model, const mbb200_opts* opts, int dev_index, int64_t N,
+                               const double* d_u0, const double* d_p, const double* saveat, int32_t n_save,
+                               double* d_out_u, double* d_out_tfinal, int32_t* d_retcode, int32_t* d_stats,
+                               double* d_reduce_out);
+
 /* Cross-process ensemble statistics: one process per GPU, the only
  * collective of the path is the sum of reduce_out over the ranks.  Rank 0 obtains an id with
  * mbb200_comm_unique_id (128 bytes, a ncclUniqueId), the launcher distributes it (the Julia glue:

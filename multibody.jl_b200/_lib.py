@@ -27,6 +27,7 @@ SYMBOLS = [
     "mbb200_solve", "mbb200_solve_device", "mbb200_model_observed_count", "mbb200_observed", "mbb200_last_timing", "mbb200_measure_fp64_peak",
     "mbb200_dev_alloc", "mbb200_dev_free", "mbb200_dev_upload", "mbb200_dev_download",
     "mbb200_host_alloc_pinned", "mbb200_host_free_pinned", "mbb200_last_error", "mbb200_shutdown",
+    "mbb200_solve_device_static",
     "mbb200_comm_unique_id", "mbb200_comm_init", "mbb200_comm_info", "mbb200_comm_allreduce", "mbb200_comm_destroy",
 ]
 
@@ -77,6 +78,8 @@ def lib() -> C.CDLL:
         L.mbb200_solve.argtypes = [vp, C.POINTER(Opts), C.c_int64, vp, vp, vp, C.c_int32, vp, vp, vp, vp, vp]
         L.mbb200_solve_device.argtypes = [vp, C.POINTER(Opts), C.c_int, C.c_int64, vp, vp, vp, C.c_int32,
                                           vp, vp, vp, vp, vp]
+        L.mbb200_solve_device_static.argtypes = [vp, C.POINTER(Opts), C.c_int, C.c_int64, vp, vp, vp, C.c_int32,
+                                                 vp, vp, vp, vp, vp]
         L.mbb200_model_observed_count.argtypes = [vp, ip]
         L.mbb200_observed.argtypes = [vp, C.c_int64, vp, vp, vp, C.c_int32, vp]
         L.mbb200_last_timing.argtypes = [C.c_int, dp, ip]

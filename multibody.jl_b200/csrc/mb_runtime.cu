@@ -82,6 +82,7 @@ struct Device {
   double last_ms = 0.0;
   int last_launches = 0;
   std::mutex mu;                    // held by the call that owns stream / queue / ws
+  unsigned char* static_scratch = nullptr;   // device address of mb_static_scratch on THIS device (mbb200_solve_device_static)
 };
 static std::vector<std::unique_ptr<Device>> g_dev;
 static std::shared_mutex g_rw;
@@ -532,6 +533,92 @@ extern "C" int mbb200_solve_device(mbb200_model* m, const mbb200_opts* o, int de
   }
   int rc2 = finish_shard(d);     // always drain what was enqueued before returning
   return rc ? rc : rc2;
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant of mbb200_solve_device (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture,
+// tight serving loops, harnesses that forbid it).
+//
+// The ensemble kernel needs two pieces of scratch memory: the trajectory work counter and a
+// device copy of the save times.  mbb200_solve_device takes them from cudaMalloc'd memory (the
+// counter at init, the save times from the grow-only workspace); here both live in ONE
+// file-scope device array of fixed size, which every GPU that loads the library holds until the
+// process exits:
+//   bytes [0, 8)                       work counter (cleared at the start of every call)
+//   bytes [256, 256 + 8 * MAX_SAVE)    save times of the current call
+// In host code `mb_static_scratch` is only a host-side stand-in for the symbol, NOT a device
+// address; the address on a given device comes from cudaGetSymbolAddress with that device
+// current (done once per device, below) and that pointer is what the kernel receives.
+// Every call shares the array and it keeps the previous call's contents, so the counter is
+// cleared on the stream first; two calls that overlap on one GPU would race on it (inside this
+// library they cannot: a call owns its device until its kernels have completed).
+// ---------------------------------------------------------------------------------------
+#define MB_STATIC_SAVE_OFFSET 256
+static __device__ __align__(256) unsigned char mb_static_scratch[MB_STATIC_SAVE_OFFSET + sizeof(double) * MBB200_STATIC_MAX_SAVE];
+
+extern "C" int mbb200_solve_device_static(mbb200_model* m, const mbb200_opts* o, int dev_index, int64_t N,
+                                          const double* d_u0, const double* d_p, const double* saveat, int32_t n_save,
+                                          double* d_out_u, double* d_tfinal, int32_t* d_rc, int32_t* d_stats,
+                                          double* d_reduce) {
+  RLock rl(g_rw);
+  int rc = check_opts(m, o, N, n_save);
+  if (rc) return rc;
+  if (dev_index < 0 || dev_index >= (int)g_dev.size()) return fail(MBB200_ERR_BAD_ARG, "bad device index %d", dev_index);
+  if (n_save > MBB200_STATIC_MAX_SAVE)
+    return fail(MBB200_ERR_BAD_ARG, "mbb200_solve_device_static: n_save = %d exceeds the static scratch limit MBB200_STATIC_MAX_SAVE = %d "
+                                    "(use mbb200_solve_device for longer save grids)", n_save, MBB200_STATIC_MAX_SAVE);
+  if (!d_u0 || !d_tfinal || !d_rc || !d_stats || (n_save > 0 && (!saveat || !d_out_u)) || (m->entry->m > 0 && !d_p))
+    return fail(MBB200_ERR_BAD_ARG, "null buffer");
+  Device& d = *g_dev[dev_index];
+  std::lock_guard<std::mutex> dl(d.mu);
+  CU(cudaSetDevice(d.ordinal));
+  if (!d.static_scratch) {                       // once per device, with that device current
+    void* ptr = nullptr;
+    CU(cudaGetSymbolAddress(&ptr, mb_static_scratch));
+    if (!ptr) return fail(MBB200_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+    d.static_scratch = (unsigned char*)ptr;
+  }
+  unsigned long long* s_queue = (unsigned long long*)d.static_scratch;
+  double* s_saveat = (double*)(d.static_scratch + MB_STATIC_SAVE_OFFSET);
+  MbArgs a;
+  a.N = N; a.u0 = d_u0; a.p = d_p; a.tb = m->d_tables[dev_index]; a.saveat = s_saveat; a.n_save = n_save;
+  a.out_u = d_out_u; a.out_tfinal = d_tfinal; a.retcode = d_rc; a.stats = d_stats; a.queue = s_queue;
+  a.t0 = o->t0; a.t1 = o->t1; a.abstol = o->abstol; a.reltol = o->reltol; a.dt0 = o->dt0; a.dtmin = o->dtmin;
+  a.dtmax = o->dtmax; a.maxiters = o->maxiters;
+  a.qs_min = o->qsteady_min; a.qs_max = o->qsteady_max; a.pow_mode = o->pow_mode;
+  if (a.qs_min == 0.0 && a.qs_max == 0.0) { a.qs_min = 1.0; a.qs_max = (o->alg == MBB200_ALG_TSIT5) ? 1.0 : 1.2; }
+  a.done = nullptr; a.flags = nullptr; a.chunk_shift = 0;
+  d.last_launches = 0;
+  d.last_ms = 0.0;
+  // the array keeps the previous call's contents: the counter must start at zero
+  CU(cudaMemsetAsync(s_queue, 0, sizeof(unsigned long long), d.stream));
+  if (n_save > 0) CU(cudaMemcpyAsync(s_saveat, saveat, sizeof(double) * n_save, cudaMemcpyHostToDevice, d.stream));
+  CU(cudaEventRecord(d.ev0, d.stream));
+  if (N > 0) {
+    cudaError_t e = m->entry->launch(o->alg, a, d.sm_count, d.stream);
+    if (e != cudaSuccess) {
+      cudaStreamSynchronize(d.stream);
+      return fail(MBB200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
+    }
+    d.last_launches++;
+    if ((o->flags & MBB200_FLAG_REDUCE) && d_reduce && n_save > 0) {   // statistic of THIS device only (no collective here)
+      const int rows = n_save * m->entry->n;
+      mb_reduce_kernel<<<rows + 1, 256, 0, d.stream>>>(d_out_u, d_rc, N, rows, d_reduce);
+      cudaError_t e2 = cudaGetLastError();
+      if (e2 != cudaSuccess) {
+        cudaStreamSynchronize(d.stream);
+        return fail(MBB200_ERR_CUDA, "statistics kernel launch failed: %s", cudaGetErrorString(e2));
+      }
+      d.last_launches++;
+    }
+  }
+  CU(cudaEventRecord(d.ev1, d.stream));
+  CU(cudaStreamSynchronize(d.stream));
+  float ms = 0.f;
+  CU(cudaEventElapsedTime(&ms, d.ev0, d.ev1));
+  d.last_ms = ms;
+  return MBB200_OK;
 }
 
 // Page-locks a caller buffer for the duration of a call when it is ordinary pageable memory
