@@ -64,8 +64,9 @@ def multibody(model: Union[str, Callable[[], ReducedSystem], ReducedSystem]) -> 
     if isinstance(model, ReducedSystem):
         return model
     if isinstance(model, str):
-        if model not in MODELS:
-            raise KeyError(f"unknown model {model!r}; available: {sorted(MODELS)}")
+        from .mechanics.chain import CHAIN_MODELS
+        if model not in MODELS and model not in CHAIN_MODELS:
+            raise KeyError(f"unknown model {model!r}; available: {sorted(MODELS) + sorted(CHAIN_MODELS)}")
         return get_model(model)
     return model()
 

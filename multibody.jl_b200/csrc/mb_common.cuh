@@ -137,6 +137,7 @@ struct MbArgs {
   unsigned* done;            // nullable
   int* flags;
   int chunk_shift;
+  double* scratch;           // kernel scratch of models that ask for it (MbKernelEntry::scratch_bytes), else null
 };
 
 // called by the thread that has just written all results of trajectory `traj`

@@ -12,6 +12,9 @@ struct MbKernelEntry {
   int nobs;             // observed (eliminated) variables the generated code can evaluate
   cudaError_t (*launch_observed)(const MbObsArgs& args, int sm_count, cudaStream_t stream);
   const MbKernelEntry* next;
+  // device scratch the kernel of `alg` needs for a shard of N trajectories on a device with sm_count SMs
+  // (0 / null for the thread-per-trajectory kernels, whose working state is registers + local memory)
+  size_t (*scratch_bytes)(int alg, long long N, int sm_count);
 };
 void mb_register_model(MbKernelEntry* e);
 const MbKernelEntry* mb_find_model(const char* name);

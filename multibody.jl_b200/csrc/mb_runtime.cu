@@ -79,6 +79,7 @@ struct Device {
   int* d_flags = nullptr;           // device alias of h_flags
   int flag_cap = 0;
   Workspace ws;
+  Workspace ws2;                    // kernel scratch of models that ask for it (MbKernelEntry::scratch_bytes)
   double last_ms = 0.0;
   int last_launches = 0;
   std::mutex mu;                    // held by the call that owns stream / queue / ws
@@ -106,6 +107,7 @@ static void destroy_device(Device& d) {
   if (d.stream) cudaStreamSynchronize(d.stream);
   if (d.cstream) cudaStreamSynchronize(d.cstream);
   if (d.ws.ptr) cudaFree(d.ws.ptr);
+  if (d.ws2.ptr) cudaFree(d.ws2.ptr);
   if (d.queue) cudaFree(d.queue);
   if (d.d_done) cudaFree(d.d_done);
   if (d.h_flags) cudaFreeHost(d.h_flags);
@@ -476,6 +478,18 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
   a.qs_min = o->qsteady_min; a.qs_max = o->qsteady_max; a.pow_mode = o->pow_mode;
   if (a.qs_min == 0.0 && a.qs_max == 0.0) { a.qs_min = 1.0; a.qs_max = (o->alg == MBB200_ALG_TSIT5) ? 1.0 : 1.2; }
   a.done = nullptr; a.flags = nullptr; a.chunk_shift = 0;
+  a.scratch = nullptr;
+  if (m->entry->scratch_bytes && Ns > 0) {        // warp-per-trajectory kernels (long ropes): W, stage vectors, sweep scratch
+    const size_t sb = m->entry->scratch_bytes(o->alg, Ns, d.sm_count);
+    if (d.ws2.bytes < sb) {
+      CU(cudaStreamSynchronize(d.stream));
+      if (d.ws2.ptr) CU(cudaFree(d.ws2.ptr));
+      d.ws2.ptr = nullptr; d.ws2.bytes = 0;
+      CU(cudaMalloc(&d.ws2.ptr, sb));
+      d.ws2.bytes = sb;
+    }
+    a.scratch = (double*)d.ws2.ptr;
+  }
   d.last_launches = 0;
   CU(cudaMemsetAsync(d.queue, 0, sizeof(unsigned long long), d.stream));
   if (stream_chunks && Ns > 0) {
@@ -570,6 +584,8 @@ extern "C" int mbb200_solve_device_static(mbb200_model* m, const mbb200_opts* o,
                                     "(use mbb200_solve_device for longer save grids)", n_save, MBB200_STATIC_MAX_SAVE);
   if (!d_u0 || !d_tfinal || !d_rc || !d_stats || (n_save > 0 && (!saveat || !d_out_u)) || (m->entry->m > 0 && !d_p))
     return fail(MBB200_ERR_BAD_ARG, "null buffer");
+  if (m->entry->scratch_bytes)
+    return fail(MBB200_ERR_UNSUPPORTED, "model '%s' needs per-warp device scratch that does not fit the static array; use mbb200_solve_device", m->entry->name);
   Device& d = *g_dev[dev_index];
   std::lock_guard<std::mutex> dl(d.mu);
   CU(cudaSetDevice(d.ordinal));
@@ -589,6 +605,7 @@ extern "C" int mbb200_solve_device_static(mbb200_model* m, const mbb200_opts* o,
   a.qs_min = o->qsteady_min; a.qs_max = o->qsteady_max; a.pow_mode = o->pow_mode;
   if (a.qs_min == 0.0 && a.qs_max == 0.0) { a.qs_min = 1.0; a.qs_max = (o->alg == MBB200_ALG_TSIT5) ? 1.0 : 1.2; }
   a.done = nullptr; a.flags = nullptr; a.chunk_shift = 0;
+  a.scratch = nullptr;
   d.last_launches = 0;
   d.last_ms = 0.0;
   // the array keeps the previous call's contents: the counter must start at zero

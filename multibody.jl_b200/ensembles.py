@@ -46,9 +46,15 @@ class EnsembleSpec:
     n_total: int             # size the BASELINE config names
 
 
-def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> EnsembleSpec:
-    """Trajectories [offset, offset+N) of config C1..C4 (N defaults to the full size)."""
+def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0, links: Optional[int] = None) -> EnsembleSpec:
+    """Trajectories [offset, offset+N) of config C1..C5 (N defaults to the full size).
+    `links` (20 or 50) selects the BASELINE-size ropes of config 5: flexible for "C5"/"C5E" (c = 800, d = 0.01),
+    stiff for "C5S"; without it C5 / C5E are the documented 6-link / 3-link ropes on the generated code path."""
     config = config.upper()
+    if links is not None:
+        if config not in ("C5", "C5E", "C5S") or links not in (20, 50):
+            raise KeyError("links = 20 or 50 applies to the rope configs C5 / C5E (flexible) and C5S (stiff)")
+        config = f"C5S{links}" if config == "C5S" else f"C5L{links}"
     if config == "C1":      # pendulum, 1024 initial angles, Tsit5 (docs/src/examples/pendulum.md:25-68)
         total, model, alg, tol = 1024, "pendulum", "tsit5", 1e-8
         saveat = np.linspace(0.0, 10.0, 101)
@@ -73,8 +79,14 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
     elif config == "C5E":   # flexible rope (c = 800, d = 0.01; ropes_and_cables.md:48-60) at the 3-link size of test/basic_tests.jl:928
         total, model, alg, tol = 1 << 16, "rope3e", "rodas5p", 1e-6
         saveat = np.linspace(0.0, 5.0, 51)[1:]
+    elif config.startswith("C5L") or config.startswith("C5S"):
+        # BASELINE.json config 5: "rope with N = 20-50 links ... warp-per-trajectory Rodas5P, 64k trajectories"; SURVEY 8d:
+        # elastic c = 800, d = 0.01, tspan (0, 5), tolerance 1e-6, 50 save points
+        nl = int(config[3:])
+        total, model, alg, tol = 1 << 16, (f"rope{nl}e" if config[2] == "L" else f"rope{nl}"), "rodas5p", 1e-6
+        saveat = np.linspace(0.0, 5.0, 51)[1:]
     else:
-        raise KeyError(f"config {config} is not built (C1..C5 are; C5 at the documented 6-link size)")
+        raise KeyError(f"config {config} is not built (C1..C5 are)")
     N = total if N is None else int(N)
     sys = get_model(model)
     idx = np.arange(offset, offset + N, dtype=np.int64)
@@ -110,6 +122,16 @@ def make_ensemble(config: str, N: Optional[int] = None, offset: int = 0) -> Ense
         P[sys.param_index("rope.d")] = 0.01
         P[sys.param_index("rope.d_joint")] = uniform(idx, 0, 0.05, 0.2)
         P[sys.param_index("body.m")] = uniform(idx, 1, 100.0, 500.0)
+        P[sys.param_index("rope.air_resistance")] = uniform(idx, 2, 0.0, 0.4)
+    elif config.startswith("C5L"):      # d_joint U[0.05,0.2], body mass U[100,500], air_resistance U[0,0.4]
+        P[sys.param_index("rope.c")] = 800.0
+        P[sys.param_index("rope.d")] = 0.01
+        P[sys.param_index("rope.d_joint")] = uniform(idx, 0, 0.05, 0.2)
+        P[sys.param_index("body.m")] = uniform(idx, 1, 100.0, 500.0)
+        P[sys.param_index("rope.air_resistance")] = uniform(idx, 2, 0.0, 0.4)
+    elif config.startswith("C5S"):      # the stiff docs rope (ropes_and_cables.md:24-36) at BASELINE length, ranges of C5
+        P[sys.param_index("rope.d_joint")] = uniform(idx, 0, 0.5, 2.0)
+        P[sys.param_index("body.m")] = uniform(idx, 1, 0.5, 2.0)
         P[sys.param_index("rope.air_resistance")] = uniform(idx, 2, 0.0, 0.4)
     elif config == "C4":
         P[sys.param_index("mechanics.load.m")] = uniform(idx, 0, 5.0, 25.0)

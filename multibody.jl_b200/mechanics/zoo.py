@@ -384,5 +384,6 @@ _cache: Dict[str, ReducedSystem] = {}
 
 def get_model(name: str) -> ReducedSystem:
     if name not in _cache:
-        _cache[name] = MODELS[name]()
+        from .chain import CHAIN_MODELS        # loop-based long ropes (not on the expression DAG)
+        _cache[name] = (MODELS[name] if name in MODELS else CHAIN_MODELS[name])()
     return _cache[name]

@@ -293,8 +293,9 @@ int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, cons
     } else {
       /* ---- Rodas5P (Appendix C.2) ---- */
       f_eval(&c, u, t, du);
-      jac_dense(&c, u, t, du, o->jac_mode, J, w1, w2, Jnz);
-      dT_eval(&c, u, t, du, o->jac_mode, dT, w2);
+      /* models without an analytic Jacobian (loop-based ropes) are differenced; they are autonomous, df/dt = 0 analytically */
+      jac_dense(&c, u, t, du, md->jac ? o->jac_mode : 1, J, w1, w2, Jnz);
+      dT_eval(&c, u, t, du, md->jac ? o->jac_mode : 0, dT, w2);
       double cg = 1.0 / (dt * T.gamma);
       for (int i = 0; i < n; i++) for (int j = 0; j < n; j++) W[i * n + j] = -J[i * n + j] + ((i == j && mass[i]) ? cg : 0.0);
       if (lu_factor(n, W, piv) != 0) { rc = RC_UNSTABLE; break; }

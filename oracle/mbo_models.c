@@ -2,10 +2,12 @@
  * Model table; one translation unit per model (mbo_model_<name>.c). */
 #include <string.h>
 #include "mbo.h"
-extern const mbo_model mbo_model_pendulum, mbo_model_spring_damper, mbo_model_robot6dof, mbo_model_fourbar, mbo_model_rope6, mbo_model_three_springs, mbo_model_fourbar_planar, mbo_model_free_couple, mbo_model_furuta, mbo_model_planar_pendulum, mbo_model_rope3e;
+extern const mbo_model mbo_model_pendulum, mbo_model_spring_damper, mbo_model_robot6dof, mbo_model_fourbar, mbo_model_rope6, mbo_model_three_springs, mbo_model_fourbar_planar, mbo_model_free_couple, mbo_model_furuta, mbo_model_planar_pendulum, mbo_model_rope3e,
+    mbo_model_rope6c, mbo_model_rope3ec, mbo_model_rope20, mbo_model_rope50, mbo_model_rope20e, mbo_model_rope50e;
 static const mbo_model* const MODELS[] = {&mbo_model_pendulum, &mbo_model_spring_damper, &mbo_model_robot6dof,
                                           &mbo_model_fourbar, &mbo_model_rope6, &mbo_model_three_springs,
-                                          &mbo_model_fourbar_planar, &mbo_model_free_couple, &mbo_model_furuta, &mbo_model_planar_pendulum, &mbo_model_rope3e};
+                                          &mbo_model_fourbar_planar, &mbo_model_free_couple, &mbo_model_furuta, &mbo_model_planar_pendulum, &mbo_model_rope3e,
+                                          &mbo_model_rope6c, &mbo_model_rope3ec, &mbo_model_rope20, &mbo_model_rope50, &mbo_model_rope20e, &mbo_model_rope50e};
 
 const mbo_model* mbo_find_model(const char* name) {
   for (unsigned i = 0; i < sizeof(MODELS) / sizeof(MODELS[0]); i++)
@@ -21,7 +23,9 @@ int mbo_model_dims(const char* name, int* n, int* m, int* nnz) {
 int mbo_eval(const char* name, int what, const double* u, const double* p, double t, const double* tb, double* out) {
   const mbo_model* md = mbo_find_model(name);
   if (!md) return -1;
-  (what == 0 ? md->rhs : what == 1 ? md->jac : what == 2 ? md->dT : md->observed)(u, p, t, tb, out);
+  mbo_fn f = (what == 0 ? md->rhs : what == 1 ? md->jac : what == 2 ? md->dT : md->observed);
+  if (!f) return -2;        /* e.g. the loop-based rope models have no analytic Jacobian */
+  f(u, p, t, tb, out);
   return 0;
 }
 int mbo_nobs(const char* name) {
@@ -42,7 +46,7 @@ int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass) {
 #include <stdlib.h>
 int mbo_factor_solve(const char* name, const double* u, const double* p, double t, const double* tb, double c, double* b) {
   const mbo_model* md = mbo_find_model(name);
-  if (!md) return -1;
+  if (!md || !md->factor) return -1;
   double* LU = (double*)calloc(md->nlu > 0 ? md->nlu : 1, sizeof(double));
   md->factor(u, p, t, tb, c, LU);
   md->solve(LU, c, p, b);

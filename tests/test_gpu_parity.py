@@ -366,3 +366,36 @@ def test_library_communicator_single_rank():
     finally:
         _lib.lib().mbb200_comm_destroy()
     assert not mbdist.comm_active()
+
+
+@pytest.mark.parametrize("config,links,N,t1", [("C5S", 20, 16, 2.0), ("C5", 20, 8, 1.0), ("C5S", 50, 4, 1.0), ("C5", 50, 2, 0.25)])
+def test_long_rope_warp_kernel_parity(oracle, config, links, N, t1):
+    """BASELINE config 5 at its named sizes (20 / 50 links, stiff and flexible): the warp-per-trajectory kernel
+    (loop-based right-hand side, forward-difference Jacobian, dense pivoted LU by the warp) against the oracle running
+    the same algorithm on the CPU.  Horizon shortened so that the oracle finishes in seconds; smooth controller on both
+    sides (the ropes are chaotic: see test_config_parity[C5E])."""
+    spec = ensembles.make_ensemble(config, N, links=links)
+    spec.tspan = (0.0, t1)
+    spec.saveat = np.linspace(0.0, t1, 11)[1:]
+    sol = _run_gpu(spec, qsteady_min=1.0, qsteady_max=1.0, exact_pow=True)
+    ref = _run_oracle(oracle, spec, nthreads=8, qsteady=(1.0, 1.0), pow_mode=1)
+    _compare(sol, ref)
+    assert np.abs(sol.stats[3] - ref["stats"][3]).max() <= 0.01 * ref["stats"][3].max() + 1    # one Jacobian per step on both sides
+    sol2 = _run_gpu(spec)                                            # default controller: same outcome class
+    assert np.all(sol2.retcode == 1)
+
+
+def test_loop_based_rope_kernel_agrees_with_the_generated_rope_kernel():
+    """Two independent GPU paths for the same 6-link rope: generated straight-line code + analytic Jacobian + structured
+    LU, one thread per trajectory (rope6) vs articulated-body sweep + forward differences + dense LU, one warp per
+    trajectory (rope6c).  Different Jacobians, so agreement is at the level of the tolerance, not of round-off."""
+    spec = ensembles.make_ensemble("C5", 64)
+    spec.tspan = (0.0, 1.0)
+    spec.saveat = np.linspace(0.0, 1.0, 6)[1:]
+    spec.abstol = spec.reltol = 1e-9
+    a = _run_gpu(spec)
+    spec.model = "rope6c"
+    b = _run_gpu(spec)
+    assert np.all(a.retcode == 1) and np.all(b.retcode == 1)
+    scale = np.maximum(np.abs(a.u).max(axis=(0, 2), keepdims=True), 1e-3)
+    assert (np.abs(a.u - b.u) / scale).max() < 1e-6
