@@ -41,6 +41,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="trajectories in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="tuning runs only: skip the host-buffer leg (the line then has no e2e)")
+    ap.add_argument("--links", type=int, default=0, help="C5 / C5S only: rope length 20 or 50 (BASELINE config 5 sizes)")
     ap.add_argument("--scaling", default="auto", choices=["auto", "strong", "weak"],
                     help="N > 1: strong = the config's ensemble (1 Mi) sharded over the ranks (BASELINE config 4, default); "
                          "weak = that many trajectories per rank")
@@ -117,8 +118,8 @@ def run_reference(args):
     from multibody_jl_b200.mechanics.zoo import get_model
     mbo.build()
     cores = os.cpu_count() or 1
-    sample = args.cpu_sample or max(256, 128 * cores)
-    spec = ensembles.make_ensemble(args.config, sample)
+    sample = args.cpu_sample or (cores * (2 if args.links <= 20 else 1) if args.links else max(256, 128 * cores))
+    spec = ensembles.make_ensemble(args.config, sample, links=args.links or None)
     tb = get_model(spec.model).tables.pack()
 
     def step():
@@ -165,7 +166,7 @@ def main():
     dev = torch.device("cuda", local)
 
     from multibody_jl_b200 import distributed as mbdist
-    spec0 = ensembles.make_ensemble(args.config, 1)
+    spec0 = ensembles.make_ensemble(args.config, 1, links=args.links or None)
     scaling = args.scaling if args.scaling != "auto" else "strong"
     if world == 1:
         scaling = "weak" if args.scaling == "auto" else scaling       # one GPU: both mean the same run
@@ -176,7 +177,7 @@ def main():
         n_job = (args.trajectories or spec0.n_total) * world
         lo, hi = rank * (n_job // world), (rank + 1) * (n_job // world)
     N = hi - lo
-    spec = ensembles.make_ensemble(args.config, N, offset=lo)
+    spec = ensembles.make_ensemble(args.config, N, offset=lo, links=args.links or None)
     sys_ = api.multibody(spec.model)
     n, m, ns = sys_.n, sys_.m, len(spec.saveat)
     ens = api.EnsembleB200(devices=[local])
@@ -331,8 +332,10 @@ def main():
         sample = args.cpu_sample or max(256, 256 * cores)
         sample = min(sample, N)
         dump = os.path.join("/tmp", f"mbb200_parity_{os.getpid()}.npz")
+        if args.links and not args.cpu_sample:      # long ropes cost seconds per trajectory on a core: one or two per thread
+            sample = min(N, cores * (2 if args.links <= 20 else 1))
         r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--config", args.config,
-                            "--steps", "1", "--warmup", "0", "--cpu-sample", str(sample), "--dump", dump],
+                            "--links", str(args.links), "--steps", "1", "--warmup", "0", "--cpu-sample", str(sample), "--dump", dump],
                            capture_output=True, text=True, env={k: v for k, v in os.environ.items()
                                                                 if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")})
         try:

@@ -92,23 +92,25 @@ MBC_FN void mbc_rot_block(const double* E, const double* M, double* o) {
  * D is ill-conditioned on a rope (bending inertia ~ m r^2 against the 0.001 twist inertia), so its inverse is never
  * formed: an explicit inverse by cofactors lost 6-8 digits here (profiles/r02_rope_long.md); triangular solves are
  * backward stable. */
+/* The diagonal of L is stored as its reciprocal (slots 0, 2, 5): the sweep applies L^-1 to nine vectors per joint,
+ * and a multiplication is worth ~10 divisions on the FP64 pipe. */
 MBC_FN void mbc_chol3(const double* D, double* L) {
-  L[0] = sqrt(D[0]);
-  L[1] = D[3] / L[0];
-  L[3] = D[6] / L[0];
-  L[2] = sqrt(D[4] - L[1] * L[1]);
-  L[4] = (D[7] - L[3] * L[1]) / L[2];
-  L[5] = sqrt(D[8] - L[3] * L[3] - L[4] * L[4]);
+  L[0] = 1.0 / sqrt(D[0]);
+  L[1] = D[3] * L[0];
+  L[3] = D[6] * L[0];
+  L[2] = 1.0 / sqrt(D[4] - L[1] * L[1]);
+  L[4] = (D[7] - L[3] * L[1]) * L[2];
+  L[5] = 1.0 / sqrt(D[8] - L[3] * L[3] - L[4] * L[4]);
 }
 MBC_FN void mbc_lsolve3(const double* L, double* x) {          /* x <- L^-1 x */
-  x[0] = x[0] / L[0];
-  x[1] = (x[1] - L[1] * x[0]) / L[2];
-  x[2] = (x[2] - L[3] * x[0] - L[4] * x[1]) / L[5];
+  x[0] = x[0] * L[0];
+  x[1] = (x[1] - L[1] * x[0]) * L[2];
+  x[2] = (x[2] - L[3] * x[0] - L[4] * x[1]) * L[5];
 }
 MBC_FN void mbc_ltsolve3(const double* L, double* x) {         /* x <- L^-T x */
-  x[2] = x[2] / L[5];
-  x[1] = (x[1] - L[4] * x[2]) / L[2];
-  x[0] = (x[0] - L[1] * x[1] - L[3] * x[2]) / L[0];
+  x[2] = x[2] * L[5];
+  x[1] = (x[1] - L[4] * x[2]) * L[2];
+  x[0] = (x[0] - L[1] * x[1] - L[3] * x[2]) * L[0];
 }
 
 #define MBC_W(j, k) ws[(size_t)((j) * MBC_LINK_DOUBLES + (k)) * stride]
@@ -242,10 +244,10 @@ MBC_FN void mbc_rope_rhs(const MbcRope* R, const double* u, int jp, double eps, 
       for (int k = 0; k < 18; k++) Y[k] = 0.0;
       mbc_mv(B, dir, t);
       mbc_mv(C, dir, t2);
-      L[0] = sqrt(dir[0] * t2[0] + dir[1] * t2[1] + dir[2] * t2[2]);
-      Y[0] = t[0] / L[0]; Y[1] = t[1] / L[0]; Y[2] = t[2] / L[0]; Y[3] = t2[0] / L[0]; Y[4] = t2[1] / L[0]; Y[5] = t2[2] / L[0];
+      L[0] = 1.0 / sqrt(dir[0] * t2[0] + dir[1] * t2[1] + dir[2] * t2[2]);       /* reciprocal, as in mbc_chol3 */
+      Y[0] = t[0] * L[0]; Y[1] = t[1] * L[0]; Y[2] = t[2] * L[0]; Y[3] = t2[0] * L[0]; Y[4] = t2[1] * L[0]; Y[5] = t2[2] * L[0];
       const double fs = -((N * p[3]) * (MBC_UK(o) - li) + (N * p[4]) * MBC_UK(o + 1));   /* Spring(c n, s_rel0 = l/n) + Damper(d n) */
-      z[0] = (fs - (dir[0] * pA[3] + dir[1] * pA[4] + dir[2] * pA[5])) / L[0];
+      z[0] = (fs - (dir[0] * pA[3] + dir[1] * pA[4] + dir[2] * pA[5])) * L[0];
     }
     for (int k = 0; k < 18; k++) MBC_W(j, MBC_U + k) = Y[k];
     for (int k = 0; k < 9; k++) MBC_W(j, MBC_DI + k) = L[k];
@@ -309,7 +311,7 @@ MBC_FN void mbc_rope_rhs(const MbcRope* R, const double* u, int jp, double eps, 
       for (int k = 0; k < 6; k++) L[k] = MBC_W(j, MBC_DI + k);
       mbc_ltsolve3(L, qdd);
     } else {
-      qdd[0] /= MBC_W(j, MBC_DI);
+      qdd[0] *= MBC_W(j, MBC_DI);
     }
     if (nd == 3) {
       for (int k = 0; k < 3; k++) {

@@ -20,6 +20,16 @@
 #include "mb_chain.h"
 #include "mb_chain_models.h"
 
+// -DMBC_PROFILE: cycle counters per phase of a warp-step, printed by the warp that retires trajectory 0 (tuning only)
+#ifdef MBC_PROFILE
+#include <cstdio>
+#define MBC_T0() long long t_ph = clock64()
+#define MBC_TICK(k) do { const long long t_now = clock64(); prof[k] += t_now - t_ph; t_ph = t_now; } while (0)
+#else
+#define MBC_T0()
+#define MBC_TICK(k)
+#endif
+
 namespace mbk {
 
 template <int NLINKS, int ELASTIC>
@@ -32,8 +42,15 @@ struct ChainDims {
   static constexpr size_t NV = ((size_t)N + 31) & ~(size_t)31;     // one state-sized vector
   static constexpr size_t VECS = 8 + 5;                            // k[8] | u | us | f0 | r | sc
   static constexpr size_t ABA = (size_t)32 * MBC_LINK_DOUBLES * NJ; // sweep scratch of the 32 lanes, lane-interleaved
+  static constexpr size_t ABA1 = (size_t)MBC_LINK_DOUBLES * NJ;      // sweep scratch of ONE evaluation (shared memory, stride 1)
   static constexpr size_t PIV = NV;                                // pivot rows (int, in a double-sized slot)
-  static constexpr size_t PER_WARP = ((W + 31) & ~(size_t)31) + VECS * NV + ABA + PIV + 32;
+  // The system is second order: half of the rows of W = M/(gamma h) - J are just c x_q - x_v = b_q.  Eliminating them
+  // exactly leaves S = c I - J_vv - J_vq / c of HALF the size (8x fewer LU flops, half-length substitution chains);
+  // G = J_vq is kept for the right-hand sides of the solves.
+  static constexpr int M = N / 2;
+  static constexpr size_t SM = ((size_t)M * M + 31) & ~(size_t)31;
+  static constexpr int MPAD = (M + 31) & ~31;
+  static constexpr size_t PER_WARP = ((W + 31) & ~(size_t)31) + 2 * SM + VECS * NV + ABA + PIV + 32;
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -42,7 +59,10 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
-// W <- LU(W) with partial pivoting (first maximum, as the oracle's lu_factor); returns false on a zero / non-finite pivot
+// S <- LU(S) with partial pivoting (first maximum, as the oracle's lu_factor); false on a zero / non-finite pivot.
+// Column-major, lanes stride over the rows of a column (coalesced).  The trailing update runs over eight columns at a
+// time so that eight independent loads are in flight per lane (one column at a time measured one memory round trip per
+// fused multiply-add, profiles/r02_rope_long.md).
 template <int N>
 __device__ bool warp_lu(double* __restrict__ Wm, int* __restrict__ piv, int lane) {
   for (int k = 0; k < N; k++) {
@@ -70,54 +90,114 @@ __device__ bool warp_lu(double* __restrict__ Wm, int* __restrict__ piv, int lane
     const double inv = 1.0 / colk[k];
     for (int i = k + 1 + lane; i < N; i += 32) colk[i] *= inv;
     __syncwarp();
-    for (int j = k + 1; j < N; j++) {
+    int j = k + 1;
+    for (; j + 7 < N; j += 8) {
+      double* c0 = Wm + (size_t)j * N;
+      double uk[8];
+#pragma unroll
+      for (int q = 0; q < 8; q++) uk[q] = c0[(size_t)q * N + k];
+      for (int i = k + 1 + lane; i < N; i += 32) {
+        const double l = colk[i];
+        double v[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) v[q] = c0[(size_t)q * N + i];
+#pragma unroll
+        for (int q = 0; q < 8; q++) c0[(size_t)q * N + i] = fma(-l, uk[q], v[q]);
+      }
+    }
+    for (; j < N; j++) {
       double* cj = Wm + (size_t)j * N;
       const double ukj = cj[k];
-      if (ukj != 0.0)
-        for (int i = k + 1 + lane; i < N; i += 32) cj[i] = fma(-colk[i], ukj, cj[i]);
+      for (int i = k + 1 + lane; i < N; i += 32) cj[i] = fma(-colk[i], ukj, cj[i]);
     }
     __syncwarp();
   }
   return true;
 }
 
-// b <- W^-1 b with the factors above (all interchanges first, then forward and backward substitution)
+// y <- S^-1 y with the factors above.  The substitution is a chain of 2 N dependent steps, so everything on the chain
+// is on chip: y and the reciprocal diagonal live in shared memory, and the column a step needs was loaded into registers
+// during the previous step (a global load inside the step measured ~900 cycles per step, profiles/r02_rope_long.md).
 template <int N>
-__device__ void warp_lu_solve(const double* __restrict__ Wm, const int* __restrict__ piv, double* __restrict__ b, int lane) {
+__device__ void warp_lu_solve(const double* __restrict__ Wm, const int* __restrict__ piv, const double* dinv, double* y, int lane) {
+  constexpr int R = (N + 31) / 32;
   if (lane == 0)
     for (int k = 0; k < N; k++) {
       const int pk = piv[k];
-      if (pk != k) { const double t = b[k]; b[k] = b[pk]; b[pk] = t; }
+      if (pk != k) { const double t = y[k]; y[k] = y[pk]; y[pk] = t; }
     }
+  double cur[R], nxt[R];
+#pragma unroll
+  for (int q = 0; q < R; q++) { const int i = lane + 32 * q; cur[q] = (i < N) ? Wm[i] : 0.0; }
   __syncwarp();
   for (int k = 0; k < N; k++) {
-    const double bk = b[k];
-    const double* colk = Wm + (size_t)k * N;
-    for (int i = k + 1 + lane; i < N; i += 32) b[i] = fma(-colk[i], bk, b[i]);
+    if (k + 1 < N) {
+      const double* cn = Wm + (size_t)(k + 1) * N;
+#pragma unroll
+      for (int q = 0; q < R; q++) { const int i = lane + 32 * q; nxt[q] = (i < N) ? cn[i] : 0.0; }
+    }
+    const double bk = y[k];
+#pragma unroll
+    for (int q = 0; q < R; q++) { const int i = lane + 32 * q; if (i > k && i < N) y[i] = fma(-cur[q], bk, y[i]); }
     __syncwarp();
+#pragma unroll
+    for (int q = 0; q < R; q++) cur[q] = nxt[q];
+  }
+  {
+    const double* c0 = Wm + (size_t)(N - 1) * N;
+#pragma unroll
+    for (int q = 0; q < R; q++) { const int i = lane + 32 * q; cur[q] = (i < N) ? c0[i] : 0.0; }
   }
   for (int k = N - 1; k >= 0; k--) {
-    const double* colk = Wm + (size_t)k * N;
-    if (lane == 0) b[k] = b[k] / colk[k];
+    if (k > 0) {
+      const double* cn = Wm + (size_t)(k - 1) * N;
+#pragma unroll
+      for (int q = 0; q < R; q++) { const int i = lane + 32 * q; nxt[q] = (i < N) ? cn[i] : 0.0; }
+    }
+    const double bk = y[k] * dinv[k];
+#pragma unroll
+    for (int q = 0; q < R; q++) { const int i = lane + 32 * q; if (i < k) y[i] = fma(-cur[q], bk, y[i]); }
     __syncwarp();
-    const double bk = b[k];
-    for (int i = lane; i < k; i += 32) b[i] = fma(-colk[i], bk, b[i]);
-    __syncwarp();
+    if (lane == 0) y[k] = bk;
+#pragma unroll
+    for (int q = 0; q < R; q++) cur[q] = nxt[q];
   }
+  __syncwarp();
 }
 
+// Degrees of freedom of the rope: dof d <-> state indices of its coordinate and of its velocity
+template <int NLINKS, int ELASTIC>
+__device__ __forceinline__ int chain_sq(int d) {
+  if (!ELASTIC) return 6 * (d / 3) + d % 3;
+  const int i = d >> 2, k = d & 3;
+  return (k < 3) ? 8 * i + k : 8 * i + 6;
+}
+template <int NLINKS, int ELASTIC>
+__device__ __forceinline__ int chain_sv(int d) {
+  if (!ELASTIC) return 6 * (d / 3) + 3 + d % 3;
+  const int i = d >> 2, k = d & 3;
+  return (k < 3) ? 8 * i + 3 + k : 8 * i + 7;
+}
 
 template <int NLINKS, int ELASTIC, class T, int BLOCK>
 __global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
   using Dm = ChainDims<NLINKS, ELASTIC>;
-  constexpr int N = Dm::N, NP = Dm::NP, NST = T::NST;
+  constexpr int N = Dm::N, NP = Dm::NP, NST = T::NST, M = Dm::M;
+  __shared__ double sh_bq[BLOCK / 32][Dm::MPAD], sh_y[BLOCK / 32][Dm::MPAD], sh_di[BLOCK / 32][Dm::MPAD];
+  extern __shared__ double mbc_dyn_smem[];      // per warp: sweep scratch of the single-lane (stage) right-hand sides
+  double* const bq = sh_bq[threadIdx.x >> 5];
+  double* const yv = sh_y[threadIdx.x >> 5];
+  double* const dinv = sh_di[threadIdx.x >> 5];
+  double* const aba1 = mbc_dyn_smem + (size_t)(threadIdx.x >> 5) * Dm::ABA1;
   constexpr double BETA1 = 7.0 / (10.0 * T::ORDER), BETA2 = 2.0 / (5.0 * T::ORDER);
   constexpr double EPS = 2.220446049250313e-16;
   const int lane = threadIdx.x & 31;
   const long long warp = ((long long)blockIdx.x * BLOCK + threadIdx.x) >> 5;
   double* const base = a.scratch + (size_t)warp * Dm::PER_WARP;
-  double* const Wm = base;
-  double* const vec = base + ((Dm::W + 31) & ~(size_t)31);
+  double* const Wm = base;                                        // raw difference columns f(u + e_j), column-major n x n
+  double* const Sm = base + ((Dm::W + 31) & ~(size_t)31);          // Schur complement / its LU, column-major M x M
+  double* const Gm = Sm + Dm::SM;                                  // J_vq, column-major M x M
+  double* const vec = Gm + Dm::SM;
   double* const K = vec;                       // k[s] = K + s * NV
   double* const u = vec + 8 * Dm::NV;
   double* const us = u + Dm::NV;
@@ -144,6 +224,9 @@ __global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
     double t = a.t0, dt, qold = QOLDINIT;
     long long iter = 0;
     int is = 0, naccept = 0, nreject = 0, nf = 0, njac = 0, nsolve = 0, rc = RC_DEFAULT;
+#ifdef MBC_PROFILE
+    long long prof[6] = {0, 0, 0, 0, 0, 0};    // fd columns | W build | LU | stage sums | stage rhs | stage solves
+#endif
     while (is < a.n_save && a.saveat[is] <= t) {
       if (a.saveat[is] == t)
         for (int i = lane; i < N; i += 32) a.out_u[((size_t)is * N + i) * a.N + traj] = u[i];
@@ -188,6 +271,7 @@ __global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
       const double cW = 1.0 / (dt * T::GAMMA), inv_dt = 1.0 / dt;
       // ---- f0 and the forward-difference Jacobian: lane L of round q evaluates column 32 q + L - 1 (column -1 = f0)
       const double rel = 1.4901161193847656e-08;          // sqrt(eps), as the oracle / FiniteDiff
+      MBC_T0();
       for (int q0 = -1; q0 < N; q0 += 32) {
         const int j = q0 + lane;
         if (j < N) {
@@ -197,13 +281,26 @@ __global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
         __syncwarp();
       }
       nf += N + 1; njac++;
-      for (int j = 0; j < N; j++) {                        // W(:, j) = -(f(u + e_j) - f0) / e_j  (+ c on the diagonal)
-        const double ej = fmax(rel * fabs(u[j]), rel);
-        double* cj = Wm + (size_t)j * N;
-        for (int i = lane; i < N; i += 32) cj[i] = -((cj[i] - f0[i]) / ej) + ((i == j) ? cW : 0.0);
+      MBC_TICK(0);
+      // S = c I - J_vv - J_vq / c and G = J_vq from the difference columns (the rows q' = v are known exactly)
+      for (int b = 0; b < M; b++) {
+        const int cq = chain_sq<NLINKS, ELASTIC>(b), cv = chain_sv<NLINKS, ELASTIC>(b);
+        const double eq = fmax(rel * fabs(u[cq]), rel), ev = fmax(rel * fabs(u[cv]), rel);
+        const double* colq = Wm + (size_t)cq * N;
+        const double* colv = Wm + (size_t)cv * N;
+        for (int a_ = lane; a_ < M; a_ += 32) {
+          const int ra = chain_sv<NLINKS, ELASTIC>(a_);
+          const double jvq = (colq[ra] - f0[ra]) / eq, jvv = (colv[ra] - f0[ra]) / ev;
+          Gm[(size_t)b * M + a_] = jvq;
+          Sm[(size_t)b * M + a_] = ((a_ == b) ? cW : 0.0) - jvv - jvq * (dt * T::GAMMA);
+        }
       }
       __syncwarp();
-      if (!warp_lu<N>(Wm, piv, lane)) { rc = RC_UNSTABLE; break; }
+      MBC_TICK(1);
+      if (!warp_lu<M>(Sm, piv, lane)) { rc = RC_UNSTABLE; break; }
+      for (int a_ = lane; a_ < M; a_ += 32) dinv[a_] = 1.0 / Sm[(size_t)a_ * M + a_];
+      __syncwarp();
+      MBC_TICK(2);
       // ---- stages
       for (int s = 0; s < NST; s++) {
         double* ks = K + (size_t)s * Dm::NV;
@@ -217,15 +314,38 @@ __global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
           us[i] = x; sc[i] = y;
         }
         __syncwarp();
+        MBC_TICK(3);
         if (s > 0) {
-          if (lane == 0) mbc_rope_rhs(&R, us, -1, 0.0, pp, ks, aba, 32);
+          if (lane == 0) mbc_rope_rhs(&R, us, -1, 0.0, pp, ks, aba1, 1);
           __syncwarp();
         }
+        MBC_TICK(4);
         for (int i = lane; i < N; i += 32) r[i] = fma(sc[i], inv_dt, (s > 0) ? ks[i] : f0[i]);   // autonomous: no df/dt term
         __syncwarp();
-        warp_lu_solve<N>(Wm, piv, r, lane);
-        for (int i = lane; i < N; i += 32) ks[i] = r[i];
+        // reduced solve: S x_v = b_v + G b_q / c,  x_q = (b_q + x_v) / c
+        for (int a_ = lane; a_ < M; a_ += 32) bq[a_] = r[chain_sq<NLINKS, ELASTIC>(a_)];
         __syncwarp();
+        for (int a_ = lane; a_ < M; a_ += 32) {
+          double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+          int b = 0;
+          for (; b + 3 < M; b += 4) {
+            acc0 = fma(Gm[(size_t)b * M + a_], bq[b], acc0);
+            acc1 = fma(Gm[(size_t)(b + 1) * M + a_], bq[b + 1], acc1);
+            acc2 = fma(Gm[(size_t)(b + 2) * M + a_], bq[b + 2], acc2);
+            acc3 = fma(Gm[(size_t)(b + 3) * M + a_], bq[b + 3], acc3);
+          }
+          for (; b < M; b++) acc0 = fma(Gm[(size_t)b * M + a_], bq[b], acc0);
+          yv[a_] = fma((acc0 + acc1) + (acc2 + acc3), dt * T::GAMMA, r[chain_sv<NLINKS, ELASTIC>(a_)]);
+        }
+        __syncwarp();
+        warp_lu_solve<M>(Sm, piv, dinv, yv, lane);
+        for (int a_ = lane; a_ < M; a_ += 32) {
+          const double xv = yv[a_];
+          ks[chain_sq<NLINKS, ELASTIC>(a_)] = (bq[a_] + xv) * (dt * T::GAMMA);
+          ks[chain_sv<NLINKS, ELASTIC>(a_)] = xv;
+        }
+        __syncwarp();
+        MBC_TICK(5);
       }
       nf += NST - 1; nsolve += NST;
       const double* k8 = K + (size_t)(NST - 1) * Dm::NV;
@@ -291,6 +411,13 @@ __global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
     __threadfence();
     __syncwarp();
     if (lane == 0) mb_retire(a, traj);
+#ifdef MBC_PROFILE
+    if (lane == 0 && traj == 0) {
+      const double st = (double)(naccept + nreject);
+      printf("MBC_PROFILE n=%d steps=%d cycles/step: fd %.0f | build %.0f | lu %.0f | sums %.0f | stage rhs %.0f | solves %.0f\n", N,
+             naccept + nreject, prof[0] / st, prof[1] / st, prof[2] / st, prof[3] / st, prof[4] / st, prof[5] / st);
+    }
+#endif
   }
 }
 

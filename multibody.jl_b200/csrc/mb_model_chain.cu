@@ -6,15 +6,24 @@
 
 #define MBC_BLOCK 64      // 2 warps = 2 trajectories per CTA; the grid is persistent (warps pull work)
 
+template <int NLINKS, int ELASTIC>
+static size_t chain_smem() { return (size_t)(MBC_BLOCK / 32) * mbk::ChainDims<NLINKS, ELASTIC>::ABA1 * sizeof(double); }
 template <int NLINKS, int ELASTIC, class T>
 static long long chain_grid(long long N, int sm_count) {
   auto kern = mbk::chain_warp_kernel<NLINKS, ELASTIC, T, MBC_BLOCK>;
   int bps = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, MBC_BLOCK, 0);
+  const size_t smem = chain_smem<NLINKS, ELASTIC>();
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, MBC_BLOCK, smem);
   const char* e = getenv("MBB200_CTAS_PER_SM");
   const int cap = e ? atoi(e) : 0;
   if (cap > 0 && cap < bps) bps = cap;
   long long grid = (long long)sm_count * (bps > 0 ? bps : 1);
+  // every warp works in ~0.5-3 MB of scratch: more resident warps hide more latency, fewer keep the scratch in the 126 MB L2.
+  // MBB200_CHAIN_CTAS overrides the number of CTAs (tuning: profiles/r02_rope_long.md)
+  const char* e2 = getenv("MBB200_CHAIN_CTAS");
+  const long long want = e2 ? atoll(e2) : 0;
+  if (want > 0 && want < grid) grid = want;
   const long long need = (N + (MBC_BLOCK / 32) - 1) / (MBC_BLOCK / 32);
   if (grid > need) grid = need;
   return grid < 1 ? 1 : grid;
@@ -30,10 +39,10 @@ static cudaError_t chain_launch(int alg, const MbArgs& a, int sm_count, cudaStre
   if (!a.scratch) return cudaErrorInvalidValue;
   if (alg == 2) {
     const long long g = chain_grid<NLINKS, ELASTIC, mbk::TabRodas5P>(a.N, sm_count);
-    mbk::chain_warp_kernel<NLINKS, ELASTIC, mbk::TabRodas5P, MBC_BLOCK><<<(unsigned)g, MBC_BLOCK, 0, st>>>(a);
+    mbk::chain_warp_kernel<NLINKS, ELASTIC, mbk::TabRodas5P, MBC_BLOCK><<<(unsigned)g, MBC_BLOCK, chain_smem<NLINKS, ELASTIC>(), st>>>(a);
   } else if (alg == 3) {
     const long long g = chain_grid<NLINKS, ELASTIC, mbk::TabRodas4>(a.N, sm_count);
-    mbk::chain_warp_kernel<NLINKS, ELASTIC, mbk::TabRodas4, MBC_BLOCK><<<(unsigned)g, MBC_BLOCK, 0, st>>>(a);
+    mbk::chain_warp_kernel<NLINKS, ELASTIC, mbk::TabRodas4, MBC_BLOCK><<<(unsigned)g, MBC_BLOCK, chain_smem<NLINKS, ELASTIC>(), st>>>(a);
   } else {
     return cudaErrorNotSupported;     // ropes are stiff: Rosenbrock methods only
   }
