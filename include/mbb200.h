@@ -81,6 +81,15 @@ typedef struct mbb200_image_header {
   int64_t n_table;      /* number of doubles of table data following the header       */
 } mbb200_image_header;
 
+/* Model image that CARRIES the model ("MBIR2"): the scheduled expression DAGs of rhs / dT / observed / factor / solve
+ * of the reduced system plus its tables -- what the Julia glue serialises from `multibody(model)` + `ODEProblem`
+ * (/root/reference/src/Multibody.jl:166-188) for a model that is not compiled into the library.  Byte layout:
+ * multibody.jl_b200/codegen/mbir.py and INTEGRATION.md.  mbb200_model_load prints it as CUDA C, appends the library's
+ * integrator templates, compiles for sm_100a with NVRTC (found at run time: libnvrtc.so.12 / $MBB200_NVRTC_LIB) and
+ * caches the cubin by image hash in $MBB200_CACHE_DIR (default ~/.cache/mbb200; MBB200_NO_CACHE=1 disables).
+ * mbb200_image_precompile does the parse + compile step alone, without a device (cache warm-up on a build machine). */
+int mbb200_image_precompile(const void* image, size_t len);
+
 int mbb200_abi_version(void);
 
 /* Initialise `n_gpus` devices (ordinals 0..n_gpus-1 of this process).  Idempotent. */

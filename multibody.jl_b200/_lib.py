@@ -27,7 +27,7 @@ SYMBOLS = [
     "mbb200_solve", "mbb200_solve_device", "mbb200_model_observed_count", "mbb200_observed", "mbb200_last_timing", "mbb200_measure_fp64_peak",
     "mbb200_dev_alloc", "mbb200_dev_free", "mbb200_dev_upload", "mbb200_dev_download",
     "mbb200_host_alloc_pinned", "mbb200_host_free_pinned", "mbb200_last_error", "mbb200_shutdown",
-    "mbb200_solve_device_static",
+    "mbb200_solve_device_static", "mbb200_image_precompile",
     "mbb200_comm_unique_id", "mbb200_comm_init", "mbb200_comm_info", "mbb200_comm_allreduce", "mbb200_comm_destroy",
 ]
 
@@ -80,6 +80,7 @@ def lib() -> C.CDLL:
                                           vp, vp, vp, vp, vp]
         L.mbb200_solve_device_static.argtypes = [vp, C.POINTER(Opts), C.c_int, C.c_int64, vp, vp, vp, C.c_int32,
                                                  vp, vp, vp, vp, vp]
+        L.mbb200_image_precompile.argtypes = [vp, C.c_size_t]
         L.mbb200_model_observed_count.argtypes = [vp, ip]
         L.mbb200_observed.argtypes = [vp, C.c_int64, vp, vp, vp, C.c_int32, vp]
         L.mbb200_last_timing.argtypes = [C.c_int, dp, ip]
@@ -117,8 +118,10 @@ def make_image(name: str, n: int, m: int, tables: np.ndarray) -> bytes:
 
 
 class ModelHandle:
-    def __init__(self, name: str, n: int, m: int, tables: np.ndarray):
-        img = make_image(name, n, m, tables)
+    def __init__(self, name: str, n: int, m: int, tables: np.ndarray, image: bytes = None):
+        """`image`: an MBIR2 image (codegen/mbir.py) that carries the model; without it an MBIR1 image naming a kernel
+        set compiled into the library is built."""
+        img = image if image is not None else make_image(name, n, m, tables)
         self._h = C.c_void_p()
         buf = C.create_string_buffer(img, len(img))
         check(lib().mbb200_model_load(buf, len(img), C.byref(self._h)))

@@ -213,7 +213,14 @@ def _ensure(ens: EnsembleB200, sys: ReducedSystem) -> _lib.ModelHandle:
     elif _devices != ords:
         raise _lib.Mbb200Error(-2, f"library already initialised on devices {_devices}; got {ords}")
     if sys.name not in _handles:
-        _handles[sys.name] = _lib.ModelHandle(sys.name, sys.n, sys.m, sys.tables.pack())
+        try:        # fast path: a kernel set compiled into the library ahead of time
+            _handles[sys.name] = _lib.ModelHandle(sys.name, sys.n, sys.m, sys.tables.pack())
+        except _lib.Mbb200Error as e:
+            if e.code != -3 or sys.meta.get("chain"):       # MBB200_ERR_UNKNOWN_MODEL
+                raise
+            # any other reduced system: the image carries the model and the library compiles it at load time (NVRTC)
+            from .codegen.mbir import serialize
+            _handles[sys.name] = _lib.ModelHandle(sys.name, sys.n, sys.m, sys.tables.pack(), image=serialize(sys))
     return _handles[sys.name]
 
 

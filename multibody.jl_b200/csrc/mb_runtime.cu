@@ -89,10 +89,15 @@ static std::vector<std::unique_ptr<Device>> g_dev;
 static std::shared_mutex g_rw;
 typedef std::shared_lock<std::shared_mutex> RLock;
 
+namespace mbjit { struct Loaded; }
 struct mbb200_model {
   const MbKernelEntry* entry;
   std::vector<double> tables;
   std::vector<double*> d_tables;   // per device
+  // models compiled at load time from an MBIR2 image (mb_jit.inc): their own descriptor and the loaded modules
+  MbKernelEntry own = {};
+  std::string own_name;
+  mbjit::Loaded* jit = nullptr;
 };
 
 extern "C" int mbb200_abi_version(void) { return MBB200_ABI_VERSION; }
@@ -195,6 +200,47 @@ static int ws_reserve(Device& d, size_t bytes) {     // caller holds d.mu
 // ---------------------------------------------------------------------------------------
 // models
 // ---------------------------------------------------------------------------------------
+// image tables: [t0, h, nk] + per table nk (value, z) pairs -> device layout of mb_common.cuh: 8-double header +
+// (nk + 1) interval rows x ntab x 4 polynomial coefficients
+static int convert_tables(const double* img, long long n_table, std::vector<double>& out) {
+  const double t0 = img[0], hh = img[1];
+  const long long nk = (long long)img[2];
+  const long long ntab = nk > 0 ? (n_table - 3) / (2 * nk) : 0;
+  if (nk < 0 || (nk > 0 && (nk < 2 || !(hh > 0.0) || 3 + 2 * nk * ntab != n_table)))
+    return fail(MBB200_ERR_BAD_ARG, "inconsistent table block (nk=%lld, n_table=%lld)", nk, n_table);
+  out.assign(MB_TB_HEADER + (size_t)(nk + 1) * ntab * 4, 0.0);
+  out[0] = t0; out[1] = hh > 0.0 ? hh : 1.0; out[2] = (double)nk; out[3] = (double)ntab;
+  for (long long k = 0; k < ntab; k++) {
+    const double* T = img + 3 + (size_t)k * 2 * nk;
+    for (long long row = 0; row <= nk; row++) {
+      double* c = out.data() + MB_TB_HEADER + ((size_t)row * ntab + k) * 4;
+      if (row == 0) { c[0] = T[0]; continue; }
+      if (row == nk) { c[0] = T[2 * (nk - 1)]; continue; }
+      const long long i = row - 1;
+      const double v0 = T[2 * i], z0 = T[2 * i + 1], v1 = T[2 * i + 2], z1 = T[2 * i + 3];
+      c[0] = v0;
+      c[1] = (v1 - v0) / hh - hh * (2.0 * z0 + z1) / 6.0;
+      c[2] = 0.5 * z0;
+      c[3] = (z1 - z0) / (6.0 * hh);
+    }
+  }
+  return MBB200_OK;
+}
+static int upload_tables(mbb200_model* m) {
+  m->d_tables.assign(g_dev.size(), nullptr);
+  for (size_t i = 0; i < g_dev.size(); i++) {
+    cudaError_t ce = cudaSetDevice(g_dev[i]->ordinal);
+    if (ce == cudaSuccess) ce = cudaMalloc(&m->d_tables[i], m->tables.size() * sizeof(double));
+    if (ce == cudaSuccess) ce = cudaMemcpy(m->d_tables[i], m->tables.data(), m->tables.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (ce != cudaSuccess) return fail(MBB200_ERR_CUDA, "table upload failed: %s", cudaGetErrorString(ce));
+  }
+  return MBB200_OK;
+}
+
+#include "mb_jit.inc"
+static int jit_model_load(const void* image, size_t len, mbb200_model** out);
+static void jit_unload(mbb200_model* m);
+
 static void model_free_locked(mbb200_model* m);
 extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** out) {
   if (!image || !out || len < sizeof(mbb200_image_header)) return fail(MBB200_ERR_BAD_ARG, "bad model image");
@@ -202,6 +248,7 @@ extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** o
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
   mbb200_image_header h;
   std::memcpy(&h, image, sizeof(h));
+  if (std::memcmp(h.magic, "MBIR2", 5) == 0) return jit_model_load(image, len, out);      // the image carries the model
   if (std::memcmp(h.magic, "MBIR1", 5) != 0) return fail(MBB200_ERR_BAD_ARG, "bad image magic");
   h.name[sizeof(h.name) - 1] = 0;
   const MbKernelEntry* e = mb_find_model(h.name);
@@ -216,33 +263,10 @@ extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** o
   }
   m->entry = e;
   {
-    // image tables: [t0, h, nk] + per table nk (value, z) pairs -> device layout of
-    // mb_common.cuh: 8-double header + (nk + 1) interval rows x ntab x 4 polynomial coefficients
     std::vector<double> img(h.n_table);
     std::memcpy(img.data(), (const char*)image + sizeof(h), (size_t)h.n_table * sizeof(double));
-    const double t0 = img[0], hh = img[1];
-    const long long nk = (long long)img[2];
-    const long long ntab = nk > 0 ? ((long long)h.n_table - 3) / (2 * nk) : 0;
-    if (nk < 0 || (nk > 0 && (nk < 2 || !(hh > 0.0) || 3 + 2 * nk * ntab != (long long)h.n_table))) {
-      delete m;
-      return fail(MBB200_ERR_BAD_ARG, "inconsistent table block (nk=%lld, n_table=%lld)", nk, (long long)h.n_table);
-    }
-    m->tables.assign(MB_TB_HEADER + (size_t)(nk + 1) * ntab * 4, 0.0);
-    m->tables[0] = t0; m->tables[1] = hh > 0.0 ? hh : 1.0; m->tables[2] = (double)nk; m->tables[3] = (double)ntab;
-    for (long long k = 0; k < ntab; k++) {
-      const double* T = img.data() + 3 + (size_t)k * 2 * nk;
-      for (long long row = 0; row <= nk; row++) {
-        double* c = m->tables.data() + MB_TB_HEADER + ((size_t)row * ntab + k) * 4;
-        if (row == 0) { c[0] = T[0]; continue; }
-        if (row == nk) { c[0] = T[2 * (nk - 1)]; continue; }
-        const long long i = row - 1;
-        const double v0 = T[2 * i], z0 = T[2 * i + 1], v1 = T[2 * i + 2], z1 = T[2 * i + 3];
-        c[0] = v0;
-        c[1] = (v1 - v0) / hh - hh * (2.0 * z0 + z1) / 6.0;
-        c[2] = 0.5 * z0;
-        c[3] = (z1 - z0) / (6.0 * hh);
-      }
-    }
+    int trc = convert_tables(img.data(), (long long)h.n_table, m->tables);
+    if (trc) { delete m; return trc; }
   }
   m->d_tables.assign(g_dev.size(), nullptr);
   for (size_t i = 0; i < g_dev.size(); i++) {
@@ -261,6 +285,7 @@ extern "C" int mbb200_model_load(const void* image, size_t len, mbb200_model** o
 
 static void model_free_locked(mbb200_model* m) {
   if (!m) return;
+  jit_unload(m);
   for (size_t i = 0; i < m->d_tables.size() && i < g_dev.size(); i++)
     if (m->d_tables[i]) {
       cudaSetDevice(g_dev[i]->ordinal);
@@ -284,6 +309,96 @@ extern "C" int mbb200_model_flops(const mbb200_model* m, int64_t flops[5]) {
   if (!m || !flops) return fail(MBB200_ERR_BAD_ARG, "null argument");
   for (int i = 0; i < 5; i++) flops[i] = m->entry->flops[i];
   return MBB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// models compiled at load time (MBIR2 images; mb_jit.inc)
+// ---------------------------------------------------------------------------------------
+static int jit_model_load(const void* image, size_t len, mbb200_model** out) {
+  mbjit::Image im;
+  int rc = mbjit::parse(image, len, im);
+  if (rc) return rc;
+  mbjit::Compiled cc;
+  rc = mbjit::compile(im, cc);                 // cache hit: no NVRTC needed
+  if (rc) return rc;
+  rc = mbjit::bind_api();                      // the driver API is needed to load the cubin either way
+  if (rc) return rc;
+  mbb200_model* m = new mbb200_model;
+  m->own_name = im.name;
+  m->own = MbKernelEntry{};
+  m->own.name = m->own_name.c_str();
+  m->own.n = im.n; m->own.m = im.m; m->own.nlu = im.nlu; m->own.is_ode = im.is_ode; m->own.nobs = im.nobs;
+  for (int k = 0; k < 5; k++) m->own.flops[k] = im.flops[k];
+  m->entry = &m->own;
+  rc = convert_tables(im.tables.data(), (long long)im.tables.size(), m->tables);
+  if (rc) { delete m; return rc; }
+  m->jit = new mbjit::Loaded;
+  m->jit->mod.assign(g_dev.size(), nullptr);
+  for (int k = 0; k < 4; k++) m->jit->fn[k].assign(g_dev.size(), nullptr);
+  rc = upload_tables(m);
+  for (size_t i = 0; rc == MBB200_OK && i < g_dev.size(); i++) {
+    cudaError_t ce = cudaSetDevice(g_dev[i]->ordinal);
+    if (ce == cudaSuccess) ce = cudaFree(0);                                    // make the primary context current
+    if (ce != cudaSuccess) { rc = fail(MBB200_ERR_CUDA, "device %d: %s", g_dev[i]->ordinal, cudaGetErrorString(ce)); break; }
+    int dr = mbjit::g_api.ModuleLoadData(&m->jit->mod[i], cc.cubin.data());
+    if (dr != 0) { rc = fail(MBB200_ERR_CUDA, "cuModuleLoadData failed (%d) for model '%s'", dr, im.name.c_str()); break; }
+    for (int k = 0; k < 4; k++)
+      if (!cc.names[k].empty()) {
+        dr = mbjit::g_api.ModuleGetFunction(&m->jit->fn[k][i], m->jit->mod[i], cc.names[k].c_str());
+        if (dr != 0) { rc = fail(MBB200_ERR_CUDA, "kernel %s not found in the compiled image (%d)", cc.names[k].c_str(), dr); break; }
+      }
+  }
+  if (rc) { model_free_locked(m); return rc; }
+  *out = m;
+  return MBB200_OK;
+}
+
+// Parse and compile an MBIR2 image into the cubin cache WITHOUT a device (warm the cache on a build machine; also what
+// the CPU-side tests exercise: NVRTC needs no GPU).
+extern "C" int mbb200_image_precompile(const void* image, size_t len) {
+  if (!image || len < 8 || std::memcmp(image, "MBIR2", 5) != 0) return fail(MBB200_ERR_BAD_ARG, "not an MBIR2 image");
+  mbjit::Image im;
+  int rc = mbjit::parse(image, len, im);
+  if (rc) return rc;
+  mbjit::Compiled cc;
+  return mbjit::compile(im, cc);
+}
+
+static void jit_unload(mbb200_model* m) {
+  if (!m->jit) return;
+  for (size_t i = 0; i < m->jit->mod.size() && i < g_dev.size(); i++)
+    if (m->jit->mod[i]) {
+      cudaSetDevice(g_dev[i]->ordinal);
+      mbjit::g_api.ModuleUnload(m->jit->mod[i]);
+    }
+  delete m->jit;
+  m->jit = nullptr;
+}
+
+// same launch geometry as MB_DEFINE_MODEL (csrc/mb_model_def.cuh): 128-thread CTAs, persistent grid
+static cudaError_t jit_launch(const mbb200_model* m, int dev_index, int alg, const MbArgs& a, int sm_count, cudaStream_t st) {
+  void* fn = (alg >= 1 && alg <= 3) ? m->jit->fn[alg - 1][dev_index] : nullptr;
+  if (!fn) return cudaErrorNotSupported;
+  int bps = 1;
+  if (mbjit::g_api.Occupancy(&bps, fn, 128, 0) != 0 || bps < 1) bps = 1;
+  long long grid = (long long)sm_count * bps;
+  const long long need = (a.N + 127) / 128;
+  if (grid > need) grid = need;
+  MbArgs args = a;
+  void* params[1] = {&args};
+  const int dr = mbjit::g_api.LaunchKernel(fn, (unsigned)grid, 1, 1, 128, 1, 1, 0, st, params, nullptr);
+  return dr == 0 ? cudaSuccess : cudaErrorLaunchFailure;
+}
+static cudaError_t jit_launch_observed(const mbb200_model* m, int dev_index, const MbObsArgs& a, int sm_count, cudaStream_t st) {
+  void* fn = m->jit->fn[3][dev_index];
+  if (!fn) return cudaErrorNotSupported;
+  long long blocks = (a.N * (long long)a.n_save + 255) / 256;
+  if (blocks > (long long)sm_count * 8) blocks = (long long)sm_count * 8;
+  if (blocks < 1) blocks = 1;
+  MbObsArgs args = a;
+  void* params[1] = {&args};
+  const int dr = mbjit::g_api.LaunchKernel(fn, (unsigned)blocks, 1, 1, 256, 1, 1, 0, st, params, nullptr);
+  return dr == 0 ? cudaSuccess : cudaErrorLaunchFailure;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -500,7 +615,7 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
   }
   CU(cudaEventRecord(d.ev0, d.stream));
   if (Ns > 0) {
-    cudaError_t e = m->entry->launch(o->alg, a, d.sm_count, d.stream);
+    cudaError_t e = m->jit ? jit_launch(m, dev_index, o->alg, a, d.sm_count, d.stream) : m->entry->launch(o->alg, a, d.sm_count, d.stream);
     if (e != cudaSuccess) return fail(MBB200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
     d.last_launches++;
     if ((o->flags & MBB200_FLAG_REDUCE) && d_reduce && n_save > 0) {
@@ -613,7 +728,7 @@ extern "C" int mbb200_solve_device_static(mbb200_model* m, const mbb200_opts* o,
   if (n_save > 0) CU(cudaMemcpyAsync(s_saveat, saveat, sizeof(double) * n_save, cudaMemcpyHostToDevice, d.stream));
   CU(cudaEventRecord(d.ev0, d.stream));
   if (N > 0) {
-    cudaError_t e = m->entry->launch(o->alg, a, d.sm_count, d.stream);
+    cudaError_t e = m->jit ? jit_launch(m, dev_index, o->alg, a, d.sm_count, d.stream) : m->entry->launch(o->alg, a, d.sm_count, d.stream);
     if (e != cudaSuccess) {
       cudaStreamSynchronize(d.stream);
       return fail(MBB200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
@@ -855,7 +970,7 @@ extern "C" int mbb200_observed(mbb200_model* m, int64_t N, const double* u, cons
     CU(cudaMemcpyAsync(d_u, u + (size_t)s0 * n * N, (size_t)ns * n * N * sizeof(double), cudaMemcpyHostToDevice, d.stream));
     MbObsArgs a;
     a.N = N; a.n_save = ns; a.u = d_u; a.p = d_p; a.tb = m->d_tables[0]; a.saveat = d_sv + s0; a.out = d_o;
-    cudaError_t e = m->entry->launch_observed(a, d.sm_count, d.stream);
+    cudaError_t e = m->jit ? jit_launch_observed(m, 0, a, d.sm_count, d.stream) : m->entry->launch_observed(a, d.sm_count, d.stream);
     if (e != cudaSuccess) return fail(MBB200_ERR_CUDA, "observed kernel launch failed: %s", cudaGetErrorString(e));
     d.last_launches++;
     CU(cudaMemcpyAsync(out_obs + (size_t)s0 * nobs * N, d_o, (size_t)ns * nobs * N * sizeof(double), cudaMemcpyDeviceToHost, d.stream));
