@@ -283,6 +283,17 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     out.append("")
+    # runtime pivot guard: the pivot ORDER is fixed at code-generation time, so the code reports the largest stored
+    # pivot reciprocal; the kernels retire a trajectory as Unstable when it is not finite or above MB_PIVOT_GUARD
+    # (a numerically singular W, e.g. a loop in a singular configuration) instead of integrating on with a bad factorisation
+    piv_slots = sorted({code.lu_slots[k] for k in code.lu_slots if k[0] == "d"})
+    out.append(f"#define MBM_{X}_NPIV {len(piv_slots)}")
+    pl = [f"MB_FN double mbm_{X}_pivmax(const double* MB_RESTRICT LU) {{", "  double g = 0.0;"]
+    for sl in piv_slots:
+        pl.append(f"  g = fmax(g, fabs(MB_LU_AT({sl})));")
+    pl += ["  return g;", "}"]
+    out.append("\n".join(pl))
+    out.append("")
     pr.smem_slots = 0
     spr = Printer(code.solve_graph, {"lu": "MB_LU_AT({i})", "b": "b{i}", "c": "c", "p": "p[{i}]"})
     sol_lines = [f"MB_FN_SOLVE void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "

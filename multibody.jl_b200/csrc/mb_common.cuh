@@ -88,6 +88,8 @@ static __constant__ double RD_H[3][8] = {
 // (beta1 = 7/(10 order), beta2 = 2/(5 order) are set per method inside the kernels)
 constexpr double SAFETY = 0.9, QMIN = 0.2, QMAX = 10.0,
                  QOLDINIT = 1e-4;
+// largest admissible |1 / pivot| of the statically ordered LU (generated pivmax()): beyond it W is numerically singular
+constexpr double MB_PIVOT_GUARD = 1e10;
 
 // `fastpower` of the reference's PI controller (FastPower.jl, formerly DiffEqBase.fastpow):
 // Float32 exp2 of y times an approximate log2 (rational fit on the significand, D. Goldberg,

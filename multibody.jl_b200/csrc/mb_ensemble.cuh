@@ -263,10 +263,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
       bool last = false;
       if (t + dt >= a.t1 - 100.0 * EPS * fabs(a.t1)) { dt = a.t1 - t; last = true; }
       double EEst;
+      bool badpiv_step = false;
       if (ROSEN) {
         // ---- Rodas5P step: W = M/(gamma dt) - J factored once, 8 stage solves ------------
         const double cW = 1.0 / (dt * T::GAMMA);
         M::factor(u, p, t, tb, cW, LU);
+        badpiv_step = !(M::pivmax(LU) <= MB_PIVOT_GUARD);      // statically ordered LU hit a numerically zero pivot
         njac++;
         if (M::HAS_DT) M::dT(u, p, t, tb, dT);
         const double inv_dt = 1.0 / dt;
@@ -335,7 +337,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) ensemble_kernel(const MbArgs a) {
         }
         EEst = scaled_rms<N>(err, u, un, a.abstol, a.reltol);
       }
-      if (!isfinite(EEst)) {
+      if (badpiv_step) {
+        rc = RC_UNSTABLE;
+      } else if (!isfinite(EEst)) {
         rc = RC_DTNAN;
       } else {
         // ---- PI controller --------------------------------------

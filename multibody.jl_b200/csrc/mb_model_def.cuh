@@ -86,6 +86,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
       mbm_##X##_solve(LU, c, p, b);                                                                 \
     }                                                                                               \
     static __device__ __forceinline__ int isdiff(int i) { return mbm_##X##_isdiff(i); }             \
+    static __device__ __forceinline__ double pivmax(const double* LU) { return mbm_##X##_pivmax(LU); } \
     static __device__ __forceinline__ void observed(const double* u, const double* p, double t,    \
                                                     const double* tb, double* o) {                  \
       mbm_##X##_observed(u, p, t, tb, o);                                                           \

@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
       if (t + dt >= a.t1 - 100.0 * EPS * fabs(a.t1)) { dt = a.t1 - t; last = true; }
       const double cW = 1.0 / (dt * T::GAMMA);
       M::factor(u, p, t, tb, cW, LU);
+      const bool badpiv = !(M::pivmax(LU) <= MB_PIVOT_GUARD);     // statically ordered LU hit a numerically zero pivot
       njac++;
       if (M::HAS_DT) {
         M::dT(u, p, t, tb, dT);
@@ -164,7 +165,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         }
         EEst = sqrt(sacc / N);
       }
-      if (!isfinite(EEst)) {
+      if (badpiv) {
+        rc = RC_UNSTABLE;
+      } else if (!isfinite(EEst)) {
         rc = RC_DTNAN;
       } else {
         double q, q11 = 0.0;

@@ -32,6 +32,7 @@ typedef struct {
   void (*solve)(const double* LU, double c, const double* p, double* b);
   int nobs;
   mbo_fn observed;
+  double (*pivmax)(const double* LU);   /* largest stored |1/pivot| of the product's statically ordered LU (tests only) */
 } mbo_model;
 
 const mbo_model* mbo_find_model(const char* name);
@@ -39,6 +40,7 @@ int mbo_model_dims(const char* name, int* n, int* m, int* nnz);
 int mbo_eval(const char* name, int what /*0 rhs,1 jac(nnz),2 dT,3 observed*/, const double* u, const double* p, double t, const double* tb, double* out);
 int mbo_factor_solve(const char* name, const double* u, const double* p, double t, const double* tb, double c, double* b);
 int mbo_pattern(const char* name, int* jrow, int* jcol, int* mass);
+double mbo_pivmax(const char* name, const double* u, const double* p, double t, const double* tb, double c);
 int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, const double* p, const double* tb,
                   double t0, double t1, const double* saveat, int nsave, double* out_u, double* out_tfinal, int32_t* stats);
 int mbo_solve_ensemble(const char* model, const mbo_opts* o, int64_t N, const double* u0, const double* p, const double* tb,

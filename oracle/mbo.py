@@ -68,6 +68,15 @@ def factor_solve(model, u, p, t, tb, c, b):
     return x
 
 
+def pivmax(model, u, p, t, tb, c):
+    """Largest |1/pivot| stored by the generated static-pivot factor() at this state (what the kernels' guard sees)."""
+    f = lib().mbo_pivmax
+    f.restype = C.c_double
+    u = np.ascontiguousarray(u, dtype=np.float64); p = np.ascontiguousarray(p, dtype=np.float64)
+    tb = np.ascontiguousarray(tb, dtype=np.float64)
+    return f(model.encode(), _dp(u), _dp(p), C.c_double(t), _dp(tb), C.c_double(c))
+
+
 def mass_diag(model):
     n, m, nnz = dims(model)
     jr = np.zeros(nnz, np.int32); jc = np.zeros(nnz, np.int32); ms = np.zeros(n, np.int32)

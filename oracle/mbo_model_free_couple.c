@@ -8,4 +8,4 @@
 #include "../multibody.jl_b200/csrc/generated/mbm_free_couple.h"
 const mbo_model mbo_model_free_couple = {"free_couple", MBM_free_couple_N, MBM_free_couple_M, MBM_free_couple_NNZ, mbm_free_couple_jrow, mbm_free_couple_jcol, mbm_free_couple_mass,
                                  mbm_free_couple_rhs, mbm_free_couple_jac, mbm_free_couple_dT, MBM_free_couple_NLU, mbm_free_couple_factor, mbm_free_couple_solve,
-                                 MBM_free_couple_NOBS, mbm_free_couple_observed};
+                                 MBM_free_couple_NOBS, mbm_free_couple_observed, mbm_free_couple_pivmax};

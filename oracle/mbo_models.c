@@ -53,3 +53,14 @@ int mbo_factor_solve(const char* name, const double* u, const double* p, double 
   free(LU);
   return 0;
 }
+
+/* largest |1/pivot| the product's generated factor() stored for this state (runtime pivot guard of the kernels) */
+double mbo_pivmax(const char* name, const double* u, const double* p, double t, const double* tb, double c) {
+  const mbo_model* md = mbo_find_model(name);
+  if (!md || !md->factor || !md->pivmax) return -1.0;
+  double* LU = (double*)calloc(md->nlu > 0 ? md->nlu : 1, sizeof(double));
+  md->factor(u, p, t, tb, c, LU);
+  const double g = md->pivmax(LU);
+  free(LU);
+  return g;
+}
