@@ -9,6 +9,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 import subprocess
+import sys
 
 import numpy as np
 
@@ -53,6 +54,8 @@ class Mbb200Error(RuntimeError):
 
 def build(verbose: bool = False) -> str:
     """Compile the library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    # the generated model headers are build output: (re)emit them when the model / generator sources changed
+    subprocess.check_call([sys.executable, os.path.join(os.path.dirname(CSRC), "codegen", "generate.py"), "--ensure"])
     subprocess.check_call(["make", "-C", CSRC, "-j8"], stdout=None if verbose else subprocess.DEVNULL)
     return LIB_PATH
 

@@ -32,5 +32,43 @@ def main(argv):
               f"F_jac={code.F_jac} F_factor={code.F_factor} F_solve={code.F_solve} -> {path}")
 
 
+def sources_hash() -> str:
+    """Hash of everything the generated headers depend on: the model front end and the code generator."""
+    import hashlib
+    h = hashlib.sha256()
+    pkg = os.path.dirname(HERE)
+    for sub in ("mechanics", "codegen"):
+        for fn in sorted(os.listdir(os.path.join(pkg, sub))):
+            if fn.endswith(".py"):
+                h.update(fn.encode())
+                h.update(open(os.path.join(pkg, sub, fn), "rb").read())
+    for k in ("MB_ROBOT_SLOTS", "MB_ROBOT_RTARGET", "MB_ROBOT_STAGE_FACTOR"):      # generator knobs
+        h.update(f"{k}={os.environ.get(k, '')}".encode())
+    return h.hexdigest()
+
+
+def ensure_generated(verbose: bool = False) -> bool:
+    """csrc/generated/ is build output (not committed): regenerate when a header is missing or the sources changed.
+    Returns True when it regenerated."""
+    outdir = os.path.join(os.path.dirname(HERE), "csrc", "generated")
+    stamp = os.path.join(outdir, ".stamp")
+    want = sources_hash()
+    have = open(stamp).read().strip() if os.path.exists(stamp) else ""
+    missing = [m for m in MODELS if not os.path.exists(os.path.join(outdir, f"mbm_{m}.h"))]
+    if have == want and not missing:
+        return False
+    if verbose:
+        print("regenerating csrc/generated (%s)" % ("missing: " + ", ".join(missing) if missing else "sources changed"))
+    import contextlib, io
+    with contextlib.redirect_stdout(sys.stdout if verbose else io.StringIO()):
+        main([])
+    with open(stamp, "w") as f:
+        f.write(want + "\n")
+    return True
+
+
 if __name__ == "__main__":
-    main(sys.argv[1:])
+    if sys.argv[1:] == ["--ensure"]:
+        ensure_generated(verbose=True)
+    else:
+        main(sys.argv[1:])

@@ -3,6 +3,7 @@ cpu_baseline / --impl reference leg).  ctypes binding of oracle/_build/libmbo.so
 import ctypes as C
 import os
 import subprocess
+import sys
 
 import numpy as np
 
@@ -23,6 +24,8 @@ class Opts(C.Structure):
 def build(force=False):
     if force and os.path.exists(LIB):
         os.remove(LIB)
+    # the oracle compiles the same generated model headers as the product: make sure they exist and are current
+    subprocess.check_call([sys.executable, os.path.join(os.path.dirname(HERE), "multibody.jl_b200", "codegen", "generate.py"), "--ensure"])
     subprocess.check_call(["make", "-C", HERE, "-j8"], stdout=subprocess.DEVNULL)   # no-op when up to date
     return LIB
 
