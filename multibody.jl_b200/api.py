@@ -65,8 +65,9 @@ def multibody(model: Union[str, Callable[[], ReducedSystem], ReducedSystem]) -> 
         return model
     if isinstance(model, str):
         from .mechanics.chain import CHAIN_MODELS
-        if model not in MODELS and model not in CHAIN_MODELS:
-            raise KeyError(f"unknown model {model!r}; available: {sorted(MODELS) + sorted(CHAIN_MODELS)}")
+        from .mechanics.zoo import IMAGE_MODELS
+        if model not in MODELS and model not in CHAIN_MODELS and model not in IMAGE_MODELS:
+            raise KeyError(f"unknown model {model!r}; available: {sorted(MODELS) + sorted(CHAIN_MODELS) + sorted(IMAGE_MODELS)}")
         return get_model(model)
     return model()
 

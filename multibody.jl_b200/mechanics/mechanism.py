@@ -45,10 +45,12 @@ class Frame:
 
 
 class Mechanism:
-    def __init__(self, mb: ModelBuilder, g: float = 9.80665, n=(0.0, -1.0, 0.0)):
-        """World defaults: src/components.jl:63 (g = 9.80665, n = [0,-1,0])."""
+    def __init__(self, mb: ModelBuilder, g: float = 9.80665, n=(0.0, -1.0, 0.0), point_gravity: bool = False, mu=3.986004418e14):
+        """World defaults: src/components.jl:63 (g = 9.80665, n = [0,-1,0]).  `point_gravity=True` selects the field
+        -mu r / |r|^3 of `gravity_acceleration` (src/components.jl:89-98), evaluated at every body's centre of mass."""
         self.mb = mb
-        self.gvec = [g * n[0], g * n[1], g * n[2]]
+        self.point_gravity, self.mu = bool(point_gravity), mu
+        self.gvec = [0.0, 0.0, 0.0] if point_gravity else [g * n[0], g * n[1], g * n[2]]
         self._back: List[Callable[[], None]] = []   # executed in reverse order
         self._eqs: List[tuple] = []                 # (accel Ex, velocity-state Ex, residual thunk)
         self._bodies: List[Callable[[], None]] = []
@@ -246,6 +248,13 @@ class Mechanism:
         def apply():
             # R (a_0 - g_0 + c |v_0| v_0) = al + c |vl| vl  (rotations preserve the norm)
             acc = fr.al
+            if self.point_gravity:
+                # Body: a_0 - gravity_acceleration(r_0 + resolve1(R, r_cm)) (src/components.jl:445-447); the base
+                # acceleration trick of the uniform field does not apply, the field depends on where the body is
+                rw = vadd(fr.r0, matTvec(fr.R, r_cm))
+                n2 = dot(rw, rw)
+                gw = vscale(-self.mu / (n2 * sqrt(n2)), rw)
+                acc = vsub(acc, matvec(fr.R, gw))
             v2 = dot(fr.vl, fr.vl)
             if not _is_zero(air_resistance) and isinstance(v2, Ex):
                 # |v| v; the 1e-300 keeps d|v|/dv = v/|v| finite (= 0) at rest, where the
@@ -267,12 +276,29 @@ class Mechanism:
         self.body(a, m, r_cm, I, air_resistance)
         return self.fixed_translation(a, r)
 
-    def line_force(self, a: Frame, b: Frame, law: Callable[[Ex, Ex], Ex]):
+    def line_force(self, a: Frame, b: Frame, law: Callable[[Ex, Ex], Ex], m=0.0, lengthfraction: float = 0.5):
         """Line force element (forces.jl:255-258, 348-354): r_rel_0 = r_b - r_a,
         s = max(|r_rel_0|, 1e-10), e = r_rel_0/s; `law(s, ds)` is the force f
         (Spring f = c (s - s0) forces.jl:392-453; Damper f = d ds :489;
-        SpringDamperParallel :524-527).  Positive f pulls the frames together."""
+        SpringDamperParallel :524-527).  Positive f pulls the frames together.
+        `m` > 0: `LineForceWithMass` (forces.jl:279-326) -- a point mass on the line at `lengthfraction` of the way from
+        frame_a to frame_b: r_CM = r_a + lengthfraction r_rel, so its acceleration is the same weighting of the two frame
+        accelerations; frame_a carries (1 - lengthfraction) m (a_CM - g), frame_b lengthfraction m (a_CM - g)."""
+        lf = float(lengthfraction)
+        has_mass = not _is_zero(m)
+
         def apply():
+            if has_mass:
+                rcm = vadd(vscale(1.0 - lf, a.r0), vscale(lf, b.r0))
+                acm = vadd(vscale(1.0 - lf, a.a0), vscale(lf, b.a0))
+                if self.point_gravity:
+                    n2 = dot(rcm, rcm)
+                    gw = vscale(-self.mu / (n2 * sqrt(n2)), rcm)
+                else:
+                    gw = self.gvec
+                ag = vsub(acm, gw)
+                a.add_wrench(matvec(a.R, vscale((1.0 - lf) * m, ag)), [0.0, 0.0, 0.0])
+                b.add_wrench(matvec(b.R, vscale(lf * m, ag)), [0.0, 0.0, 0.0])
             rrel = vsub(b.r0, a.r0)
             length = sqrt(dot(rrel, rrel))
             s = fmax(length, 1e-10)

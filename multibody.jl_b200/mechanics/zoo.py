@@ -366,6 +366,48 @@ def fourbar_planar() -> ReducedSystem:
     return sysm
 
 
+def point_gravity_two_bodies() -> ReducedSystem:
+    """test/basic_tests.jl:124-168: two free root bodies (Euler-angle roots, m = 1, I = 0.1) in the point gravity field
+    of `World(point_gravity = true, mu = 1)` (src/components.jl:89-98); the reference asserts body2.r_0(5)."""
+    mb = ModelBuilder("point_gravity")
+    mu = mb.param("world.mu", 1.0)
+    mech = Mechanism(mb, point_gravity=True, mu=mu)
+    for k, (r, v) in enumerate((((0.0, 0.6, 0.0), (1.0, 0.0, 0.0)), ((0.6, 0.6, 0.0), (0.6, 0.0, 0.0)))):
+        nm = f"body{k+1}"
+        r0 = [mb.state(f"{nm}.r_0[{i+1}]", x) for i, x in enumerate(r)]
+        v0 = [mb.state(f"{nm}.v_0[{i+1}]", x) for i, x in enumerate(v)]
+        phi = [mb.state(f"{nm}.phi[{i+1}]", 0.0) for i in range(3)]
+        phid = [mb.state(f"{nm}.phid[{i+1}]", 0.0) for i in range(3)]
+        b = mech.free_body_euler(r0, v0, phi, phid)
+        mech.body(b, 1.0, (0.0, 0.0, 0.0), (0.1, 0.1, 0.1, 0.0, 0.0, 0.0))
+    mech.solve_accelerations()
+    return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+
+
+def spring_with_mass() -> ReducedSystem:
+    """`Spring(c, m)` = `LineForceWithMass` (src/forces.jl:279-326, used by docs/src/examples/swing.md:27): a body on a
+    vertical `Prismatic` hangs from the world by a spring that carries a point mass at its middle (lengthfraction 1/2).
+    Closed form (Lagrange, the point mass moves with half the joint speed):
+    (M + m_s / 4) s'' = M g + m_s g / 2 - c (s - s0)."""
+    mb = ModelBuilder("spring_with_mass")
+    mech = Mechanism(mb)
+    c = mb.param("spring.c", 40.0)
+    ms = mb.param("spring.m", 0.5)
+    M = mb.param("body.m", 1.0)
+    s = mb.state("joint.s", 0.3)
+    v = mb.state("joint.v", 0.0)
+    w = mech.world()
+    pj = mech.prismatic(w, (0.0, -1.0, 0.0), s, v, name="joint")
+    mech.body(pj, M, (0.0, 0.0, 0.0))
+    mech.line_force(w, pj, lambda sl, ds: c * (sl - 0.1), m=ms, lengthfraction=0.5)
+    mech.solve_accelerations()
+    return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+
+
+# models that are not compiled into the library: they reach the device through an MBIR2 image that carries them
+# (codegen/mbir.py; compiled at load time)
+IMAGE_MODELS: Dict[str, Callable[[], ReducedSystem]] = {"point_gravity": point_gravity_two_bodies, "spring_with_mass": spring_with_mass}
+
 MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "pendulum": pendulum,
     "spring_damper": spring_damper,
@@ -385,5 +427,5 @@ _cache: Dict[str, ReducedSystem] = {}
 def get_model(name: str) -> ReducedSystem:
     if name not in _cache:
         from .chain import CHAIN_MODELS        # loop-based long ropes (not on the expression DAG)
-        _cache[name] = (MODELS[name] if name in MODELS else CHAIN_MODELS[name])()
+        _cache[name] = (MODELS[name] if name in MODELS else IMAGE_MODELS[name] if name in IMAGE_MODELS else CHAIN_MODELS[name])()
     return _cache[name]

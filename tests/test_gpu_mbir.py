@@ -72,3 +72,26 @@ def test_cpp_driver_of_the_abi_loads_the_image_and_agrees_with_the_python_host(t
     ep = api.EnsembleProblem(api.ODEProblem(s, tspan=(0.0, 2.0)), u0_matrix=U, p_matrix=P)
     sol = api.solve(ep, api.Rodas5P(), api.EnsembleB200(), trajectories=N, saveat=sv, abstol=1e-8, reltol=1e-8)
     assert np.array_equal(sol.u, u)                      # same image, same library: bit-identical
+
+
+def test_image_models_point_gravity_and_spring_with_mass(tmp_path, monkeypatch):
+    """The component variants of tests/test_components_extra.py on the device (carried by their images): point gravity
+    (test/basic_tests.jl:124-168) and `Spring(c, m)` / `LineForceWithMass` (src/forces.jl:279-326)."""
+    monkeypatch.setenv("MBB200_CACHE_DIR", str(tmp_path / "cache"))
+    from scipy.integrate import solve_ivp
+    for name, t1 in (("point_gravity", 5.0), ("spring_with_mass", 3.0)):
+        s = api.multibody(name)
+        N = 40
+        rng = np.random.default_rng(6)
+        U = np.repeat(np.array(s.u0, float)[:, None], N, axis=1)
+        P = np.repeat(np.array(s.p0, float)[:, None], N, axis=1) * (1.0 + 0.2 * rng.random((s.m, N)))
+        P[:, 0] = s.p0
+        sv = np.array([0.5 * t1, t1])
+        ep = api.EnsembleProblem(api.ODEProblem(s, tspan=(0.0, t1)), u0_matrix=U, p_matrix=P)
+        sol = api.solve(ep, api.Tsit5(), api.EnsembleB200(), trajectories=N, saveat=sv, abstol=1e-10, reltol=1e-10)
+        assert np.all(sol.retcode == 1)
+        for j in (0, 13):
+            ref = solve_ivp(lambda t, u: s.eval_rhs(u, P[:, j], t), (0.0, t1), U[:, j], method="DOP853", rtol=1e-11, atol=1e-13, t_eval=sv)
+            assert np.abs(sol.u[:, :, j] - ref.y.T).max() < 1e-7, (name, j)
+    s = api.multibody("point_gravity")
+    assert abs(sol.u.shape[1] - 2) == 0                      # (last loop item was the 2-state spring)
