@@ -180,6 +180,37 @@ class Mechanism:
             mb.set_rhs(phi[i], phid[i])
         return b
 
+    def spherical_quat(self, a: Frame, Qh: Sequence[Ex], w: Sequence[Ex], d=0.0, k: float = 0.1) -> Frame:
+        """Spherical(state=true, quat=true) (joints.jl:226-233): the relative orientation is the non-unit quaternion of
+        orientation.jl:438-472 -- D(Qhat) = Omega(w_rel) Qhat / 2 + k (1 - Qhat'Qhat) Qhat, Rrel = from_Q(Qhat / |Qhat|) --
+        and the states are Qhat[4] and w_rel[3] (resolved in frame_b); no Euler-angle singularity."""
+        mb = self.mb
+        n = Qh[0] * Qh[0] + Qh[1] * Qh[1] + Qh[2] * Qh[2] + Qh[3] * Qh[3]
+        c = k * (1.0 - n)
+        Om = [[0.0, -w[0], -w[1], -w[2]], [w[0], 0.0, w[2], -w[1]], [w[1], -w[2], 0.0, w[0]], [w[2], w[1], -w[0], 0.0]]
+        for i in range(4):
+            acc = c * Qh[i]
+            for j in range(4):
+                if not (isinstance(Om[i][j], float) and Om[i][j] == 0.0):
+                    acc = acc + 0.5 * (Om[i][j] * Qh[j])
+            mb.set_rhs(Qh[i], acc)
+        rn = 1.0 / sqrt(n)
+        Rrel = from_Q([q * rn for q in Qh])
+        accs = [mb.accel() for _ in range(3)]
+        wrel = list(w)
+        Rw = matvec(Rrel, a.w)
+        wb = vadd(Rw, wrel)
+        zb = vadd(vsub(matvec(Rrel, a.z), cross(wrel, Rw)), accs)
+        b = Frame(a.r0, matmul(Rrel, a.R), wb, a.v0, a.a0, zb, matvec(Rrel, a.vl), matvec(Rrel, a.al))
+
+        def back():
+            a.add_wrench(matTvec(Rrel, b.f), matTvec(Rrel, b.tau))
+        self._back.append(back)
+        fric = matvec(Rrel, vscale(d, wrel)) if not _is_zero(d) else [0.0, 0.0, 0.0]    # resolved as joints.jl:218-222
+        for i in range(3):
+            self._eqs.append((accs[i], w[i], (lambda i=i: vadd(b.tau, fric)[i]), {}))
+        return b
+
     def free_body_euler(self, r0: Sequence[Ex], v0: Sequence[Ex], phi: Sequence[Ex],
                         phid: Sequence[Ex], seq=(1, 2, 3)) -> Frame:
         """Root `Body(isroot=true)` with Euler angles (components.jl:420-434): states

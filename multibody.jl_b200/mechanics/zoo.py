@@ -404,9 +404,33 @@ def spring_with_mass() -> ReducedSystem:
     return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
 
 
+def spherical_pendulum(quat: bool) -> ReducedSystem:
+    """test/basic_tests.jl:1170-1227: `World -> Spherical(state=true, quat) -> FixedTranslation(r=[1,0,0]) -> Body(m=1)`;
+    the reference asserts that the quaternion and the Euler-angle joint give the same body.r_0 on 0:0.1:1 (rtol 1e-5)."""
+    mb = ModelBuilder("spherical_pendulum_quat" if quat else "spherical_pendulum_euler")
+    mech = Mechanism(mb)
+    if quat:
+        Qh = [mb.state(f"joint.Qhat[{i+1}]", 1.0 if i == 0 else 0.0) for i in range(4)]
+        w = [mb.state(f"joint.w_rel[{i+1}]", 0.0) for i in range(3)]
+        jb = mech.spherical_quat(mech.world(), Qh, w)
+    else:
+        phi = [mb.state(f"joint.phi[{i+1}]", 0.0) for i in range(3)]
+        phid = [mb.state(f"joint.phid[{i+1}]", 0.0) for i in range(3)]
+        jb = mech.spherical(mech.world(), phi, phid)
+    fr = mech.fixed_translation(jb, (1.0, 0.0, 0.0))
+    mech.body(fr, 1.0, (0.0, 0.0, 0.0))
+    for c in range(3):
+        v = fr.r0[c]
+        mb.observed[f"body.r_0[{c+1}]"] = v.n if hasattr(v, "n") else mb.const(float(v)).n
+    mech.solve_accelerations()
+    return mb.finish(tspan=(0.0, 1.0), mechanism=mech)
+
+
 # models that are not compiled into the library: they reach the device through an MBIR2 image that carries them
 # (codegen/mbir.py; compiled at load time)
-IMAGE_MODELS: Dict[str, Callable[[], ReducedSystem]] = {"point_gravity": point_gravity_two_bodies, "spring_with_mass": spring_with_mass}
+IMAGE_MODELS: Dict[str, Callable[[], ReducedSystem]] = {"point_gravity": point_gravity_two_bodies, "spring_with_mass": spring_with_mass,
+                                                        "spherical_pendulum_quat": lambda: spherical_pendulum(True),
+                                                        "spherical_pendulum_euler": lambda: spherical_pendulum(False)}
 
 MODELS: Dict[str, Callable[[], ReducedSystem]] = {
     "pendulum": pendulum,

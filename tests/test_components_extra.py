@@ -32,3 +32,24 @@ def test_spring_with_point_mass_closed_form():
         du = s.eval_rhs(np.array([sj, vj]), np.array([c, ms, M]), 0.0)
         want = (M * g + ms * g / 2 - c * (sj - 0.1)) / (M + ms / 4)
         assert abs(du[0] - vj) < 1e-14 and abs(du[1] - want) < 1e-12 * max(1.0, abs(want))
+
+
+def test_quaternion_and_euler_spherical_joints_agree():
+    """test/basic_tests.jl:1170-1227 (`Spherical(state=true, quat=true)` vs `quat=false`, body.r_0 on 0:0.1:1, rtol 1e-5);
+    also released with an out-of-plane spin so that all three rotational degrees of freedom move."""
+    q, e = api.multibody("spherical_pendulum_quat"), api.multibody("spherical_pendulum_euler")
+    assert q.n == 7 and e.n == 6
+    tv = np.linspace(0.0, 1.0, 11)
+    for spin in (0.0, 1.5):
+        uq, ue = np.array(q.u0, float), np.array(e.u0, float)
+        uq[q.state_index("joint.w_rel[2]")] = spin            # w_rel about the local y axis ...
+        ue[e.state_index("joint.phid[2]")] = spin             # ... equals phid[2] at phi = 0
+        out = []
+        for s, u0 in ((q, uq), (e, ue)):
+            sol = solve_ivp(lambda t, u: s.eval_rhs(u, s.p0, t), (0.0, 1.0), u0, method="DOP853", rtol=1e-10, atol=1e-12, t_eval=tv)
+            names = s.observed_names
+            obs = np.array([s.g.evaluate([s.observed[k] for k in names], {**{("u", i): sol.y[i, j] for i in range(s.n)}, ("t", 0): tv[j]}, s.tables)
+                            for j in range(len(tv))])
+            out.append(obs)
+        assert np.abs(out[0] - out[1]).max() < 1e-7, spin
+        assert abs(np.linalg.norm(out[0][-1]) - 1.0) < 1e-8     # the rod keeps its length (basic_tests.jl:621-622)
