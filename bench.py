@@ -122,9 +122,14 @@ def run_reference(args):
     spec = ensembles.make_ensemble(args.config, sample, links=args.links or None)
     tb = get_model(spec.model).tables.pack()
 
+    # the ropes' generated oracle units are compiled at -O0 (198k lines: -O1 takes 5.5 min of gcc); the loop-based code of
+    # the same equations (csrc/mb_chain.h, -O2, finite-difference Jacobian as the reference's rope examples use) is 7x
+    # faster on the CPU (profiles/r02_rope_long.md) and is therefore the CPU arm of C5 / C5E
+    cpu_model = {"rope6": "rope6c", "rope3e": "rope3ec"}.get(spec.model, spec.model)
+
     def step():
         t = time.perf_counter()
-        r = mbo.solve(spec.model, spec.alg, spec.u0, spec.p, tb, spec.tspan, spec.saveat, abstol=spec.abstol,
+        r = mbo.solve(cpu_model, spec.alg, spec.u0, spec.p, tb, spec.tspan, spec.saveat, abstol=spec.abstol,
                       reltol=spec.reltol, nthreads=cores)
         dt_ = time.perf_counter() - t
         assert (r["retcode"] == 1).all()
@@ -142,6 +147,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(spec, full), "sample": sample},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                         "model": cpu_model,
                          "sample": f"first {sample} trajectories of the same workload per step (same RNG stream), all {cores} host threads, "
                                    f"{dt / args.steps:.1f} s per step"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
