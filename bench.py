@@ -257,15 +257,24 @@ def main():
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath)).get(spec.config)
-        if tj:
+        # a measured-traffic entry is only used for the kernel it was captured on: the kernel string must name this
+        # model (or this rope length) and this solver's tableau; anything else is stale and `traffic` stays null
+        chain = sys_.meta.get("chain")
+        want = (f"chain_warp_kernel<{chain[0]}, {int(chain[1])}," if chain else f"MbModel_{spec.model},")
+        tab = {"rodas5p": ("TabRodas5P", ", 2,"), "rodas4": ("TabRodas4", ", 3,"), "tsit5": (", 1,",)}[spec.alg]
+        if tj and want in tj.get("kernel", "") and any(x in tj["kernel"] for x in tab):
             traffic = tj["dram_bytes_per_trajectory"] * N
             peak_hbm = 6530.6
             ppath = os.path.join(ROOT, "MEASURED_PEAKS.json")
             if os.path.exists(ppath):
                 peak_hbm = json.load(open(ppath)).get("hbm_gbs", peak_hbm)
             gbs = traffic * args.steps / (dev_ms * 1e-3) / 1e9
-            hbm = {"achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm,
-                   "note": "thread-local working state spilling past the 126 MB L2 (not algorithmic traffic)"}
+            hbm = {"achieved": gbs, "peak": peak_hbm, "unit": "GB/s", "frac": gbs / peak_hbm, "kernel": tj["kernel"],
+                   "note": "ncu dram bytes per trajectory of this kernel (profiles/r02_ncu_summary.md) x trajectories / launch time: "
+                           "thread-local / per-warp working state cycling through the L2, not algorithmic traffic"}
+        elif tj:
+            print(f"bench: profiles/traffic.json[{spec.config}] was captured on '{tj.get('kernel')}', not on this kernel; traffic = null",
+                  file=sys.stderr)
 
     # ---- end to end through the host-buffer ABI call (pinned host memory) ----------------------
     h_u0 = torch.from_numpy(spec.u0).pin_memory()

@@ -5,7 +5,7 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
-enum { MBO_ALG_TSIT5 = 1, MBO_ALG_RODAS5P = 2, MBO_ALG_RODAS4 = 3 };
+enum { MBO_ALG_TSIT5 = 1, MBO_ALG_RODAS5P = 2, MBO_ALG_RODAS4 = 3, MBO_ALG_FBDF = 4 };
 typedef struct {
   int32_t alg;        /* MBO_ALG_* */
   int32_t jac_mode;   /* 0 analytic (generated), 1 forward differences (`autodiff=false`, test/test_robot.jl:288) */

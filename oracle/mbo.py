@@ -9,7 +9,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "_build", "libmbo.so")
-ALG = {"tsit5": 1, "rodas5p": 2, "rodas4": 3}
+ALG = {"tsit5": 1, "rodas5p": 2, "rodas4": 3, "fbdf": 4}
 _lib = None
 
 

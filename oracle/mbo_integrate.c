@@ -191,9 +191,12 @@ static void dT_eval(ctx_t* c, const double* u, double t, const double* f0, int m
   for (int i = 0; i < n; i++) dT[i] = (wf[i] - f0[i]) / eps;
 }
 
+#include "mbo_bdf.inc"
+
 int mbo_solve_one(const mbo_model* md, const mbo_opts* o, const double* u0, const double* p, const double* tb,
                   double t0, double t1, const double* saveat, int nsave, double* out_u /* [nsave][n] */,
                   double* out_tfinal, int32_t* stats /* [5] */) {
+  if (o->alg == MBO_ALG_FBDF) return bdf_solve_one(md, o, u0, p, tb, t0, t1, saveat, nsave, out_u, out_tfinal, stats);
   const int n = md->n;
   ctx_t c = {md, p, tb, n, 0, 0, 0, 0, 0};
   const int rosen = (o->alg == MBO_ALG_RODAS5P || o->alg == MBO_ALG_RODAS4);
