@@ -37,6 +37,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="C4")
+    ap.add_argument("--alg", default="", choices=["", "tsit5", "rodas5p", "rodas4", "fbdf"],
+                    help="solver override (default: the config's own; the headline metric is quoted on the default)")
     ap.add_argument("--trajectories", type=int, default=0, help="per-GPU ensemble size (0 = the config's full size)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="trajectories in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -98,9 +100,18 @@ def flops_per_trajectory(flops, n, n_save, stats, alg="rodas5p"):
         f_step = dense_step = 6 * flops["rhs"] + 56 * n
         f_interp = (7 * 2 + 7 * 8 + 2) * n
         return steps * f_step + n_save * f_interp + 3 * flops["rhs"], f_step, dense_step, steps
-    f_step = flops["factor"] + flops["dT"] + 8 * flops["rhs"] + 8 * flops["solve"] + 86 * n + 4 * n
+    if alg == "fbdf":
+        # per step attempt: one factor (jac + LU); per Newton iteration (= linear solve, stats[4]): rhs + solve + 8 n;
+        # predictor / differences / error norms ~ 40 n
+        iters = stats[4].astype(np.float64)
+        f_step = flops["factor"] + 40 * n
+        dense_step = flops["jac"] + (2 * n ** 3) // 3 + 40 * n
+        per_it = flops["rhs"] + flops["solve"] + 8 * n
+        return steps * f_step + iters * per_it + n_save * 12 * n + 3 * flops["rhs"], f_step, dense_step, steps
+    nst = 6 if alg == "rodas4" else 8
+    f_step = flops["factor"] + flops["dT"] + nst * flops["rhs"] + nst * flops["solve"] + 86 * n + 4 * n
     f_interp = (8 * 3 * 2 + 10) * n
-    dense_step = flops["jac"] + flops["dT"] + (2 * n ** 3) // 3 + 8 * flops["rhs"] + 16 * n * n + 86 * n + 4 * n
+    dense_step = flops["jac"] + flops["dT"] + (2 * n ** 3) // 3 + nst * flops["rhs"] + 2 * nst * n * n + 86 * n + 4 * n
     return steps * f_step + n_save * f_interp + 2 * flops["rhs"], f_step, dense_step, steps
 
 
@@ -120,6 +131,7 @@ def run_reference(args):
     cores = os.cpu_count() or 1
     sample = args.cpu_sample or (cores * (2 if args.links <= 20 else 1) if args.links else max(256, 128 * cores))
     spec = ensembles.make_ensemble(args.config, sample, links=args.links or None)
+    spec.alg = args.alg or spec.alg
     tb = get_model(spec.model).tables.pack()
 
     # the ropes' generated oracle units are compiled at -O0 (198k lines: -O1 takes 5.5 min of gcc); the loop-based code of
@@ -173,6 +185,7 @@ def main():
 
     from multibody_jl_b200 import distributed as mbdist
     spec0 = ensembles.make_ensemble(args.config, 1, links=args.links or None)
+    spec0.alg = args.alg or spec0.alg
     scaling = args.scaling if args.scaling != "auto" else "strong"
     if world == 1:
         scaling = "weak" if args.scaling == "auto" else scaling       # one GPU: both mean the same run
@@ -184,6 +197,7 @@ def main():
         lo, hi = rank * (n_job // world), (rank + 1) * (n_job // world)
     N = hi - lo
     spec = ensembles.make_ensemble(args.config, N, offset=lo, links=args.links or None)
+    spec.alg = args.alg or spec.alg
     sys_ = api.multibody(spec.model)
     n, m, ns = sys_.n, sys_.m, len(spec.saveat)
     ens = api.EnsembleB200(devices=[local])
@@ -197,7 +211,7 @@ def main():
             return box[0]
         mbdist.comm_init(rank, world, bcast)
     flops = h.flops()
-    alg = api.Tsit5() if spec.alg == "tsit5" else api.Rodas5P()
+    alg = {"tsit5": api.Tsit5(), "rodas5p": api.Rodas5P(), "rodas4": api.Rodas4(), "fbdf": api.FBDF()}[spec.alg]
     opts = api.make_opts(alg, spec.tspan, spec.abstol, spec.reltol, reduce=True)
     L = _lib.lib()
 
@@ -261,7 +275,7 @@ def main():
         # model (or this rope length) and this solver's tableau; anything else is stale and `traffic` stays null
         chain = sys_.meta.get("chain")
         want = (f"chain_warp_kernel<{chain[0]}, {int(chain[1])}," if chain else f"MbModel_{spec.model},")
-        tab = {"rodas5p": ("TabRodas5P", ", 2,"), "rodas4": ("TabRodas4", ", 3,"), "tsit5": (", 1,",)}[spec.alg]
+        tab = {"rodas5p": ("TabRodas5P", ", 2,"), "rodas4": ("TabRodas4", ", 3,"), "tsit5": (", 1,",), "fbdf": ("bdf_kernel",)}[spec.alg]
         if tj and want in tj.get("kernel", "") and any(x in tj["kernel"] for x in tab):
             traffic = tj["dram_bytes_per_trajectory"] * N
             peak_hbm = 6530.6

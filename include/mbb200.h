@@ -29,8 +29,10 @@ extern "C" {
 
 #define MBB200_ABI_VERSION 2
 
-/* algorithm ids (OrdinaryDiffEq names: Tsit5(), Rodas5P(), Rodas4()) */
-enum { MBB200_ALG_TSIT5 = 1, MBB200_ALG_RODAS5P = 2, MBB200_ALG_RODAS4 = 3 };
+/* algorithm ids (OrdinaryDiffEq names: Tsit5(), Rodas5P(), Rodas4(), FBDF()).
+ * FBDF (test/test_fourbar.jl:45,71) is served by a variable-order BDF in the published NDF formulation: the same
+ * method family and tolerances, not the step sequence of OrdinaryDiffEqBDF. */
+enum { MBB200_ALG_TSIT5 = 1, MBB200_ALG_RODAS5P = 2, MBB200_ALG_RODAS4 = 3, MBB200_ALG_FBDF = 4 };
 
 /* SciMLBase.ReturnCode values written to retcode[] */
 enum {

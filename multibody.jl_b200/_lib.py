@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MBB200_LIB") or os.path.join(HERE, "lib", "libmultibody_b200.so")
 CSRC = os.path.join(HERE, "csrc")
 
-ALG_TSIT5, ALG_RODAS5P, ALG_RODAS4 = 1, 2, 3
+ALG_TSIT5, ALG_RODAS5P, ALG_RODAS4, ALG_FBDF = 1, 2, 3, 4
 FLAG_REDUCE = 1
 RC_NAMES = {0: "Default", 1: "Success", 3: "DtNaN", 4: "MaxIters", 5: "DtLessThanMin", 6: "Unstable"}
 

@@ -45,6 +45,17 @@ class Rodas4:
     id: int = _lib.ALG_RODAS4
 
 
+@dataclass(frozen=True)
+class FBDF:
+    """The solver of the reference's loop examples (test/test_fourbar.jl:45,71 `FBDF(autodiff=true)`;
+    docs/src/examples/kinematic_loops.md:80,152,190).  Served by a variable-order BDF (orders 1-5) in the published NDF
+    formulation -- the same method family at the same tolerances, not OrdinaryDiffEqBDF's step sequence (DESIGN.md
+    section 4).  Models rope6 / rope3e / robot6dof and the long ropes are built without this kernel
+    (error MBB200_ERR_UNSUPPORTED)."""
+    autodiff: bool = True
+    id: int = _lib.ALG_FBDF
+
+
 @dataclass
 class EnsembleB200:
     """The new `SciMLBase.EnsembleAlgorithm`.  `devices`: CUDA ordinals used by this

@@ -4,6 +4,7 @@
 #pragma once
 #include "mb_ensemble.cuh"
 #include "mb_rodas_rows.cuh"
+#include "mb_bdf.cuh"
 #include "mb_registry.h"
 #include <cstdlib>
 
@@ -59,6 +60,22 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #endif
 // shared-memory carve-out in percent of the 228 KB maximum: what the kernel needs, the rest stays L1
 static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 233471) / 233472) : 0; }
+// alg 4 (FBDF): one more instantiation of the generated functions per model; a translation unit whose compile time
+// cannot afford it defines MB_NO_BDF and the launcher then answers cudaErrorInvalidValue for alg 4
+#ifdef MB_NO_BDF
+#define MB_BDF_LAUNCH(MODEL, BLOCK, MINB) return cudaErrorInvalidValue;
+#else
+#define MB_BDF_LAUNCH(MODEL, BLOCK, MINB)                                                             \
+  auto kern = mbk::bdf_kernel<MODEL, BLOCK, MINB>;                                                    \
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);                 \
+  cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem));      \
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, kern, BLOCK, smem);                             \
+  bps = mb_cap_ctas_per_sm(bps);                                                                      \
+  long long grid = (long long)sm_count * (bps > 0 ? bps : 1);                                         \
+  long long need = (a.N + BLOCK - 1) / BLOCK;                                                         \
+  if (grid > need) grid = need;                                                                       \
+  kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);
+#endif
 
 #define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
   struct MbModel_##X {                                                                              \
@@ -128,6 +145,8 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
       long long need = (a.N + BLOCK - 1) / BLOCK;                                                   \
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
+    } else if (alg == 4) {                                                                          \
+      MB_BDF_LAUNCH(MbModel_##X, BLOCK, MINB)                                                       \
     } else {                                                                                        \
       return cudaErrorInvalidValue;                                                                 \
     }                                                                                               \

@@ -5,6 +5,7 @@
 #if MB_ROWS_SMEM == 2
 #define MB_RHS_STRIDED
 #endif
+#define MB_NO_BDF   // no FBDF kernel for this model (compile time; the reference uses FBDF on its loop examples only)
 #include "mb_model_def.cuh"
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__

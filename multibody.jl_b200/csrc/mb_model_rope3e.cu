@@ -8,6 +8,7 @@
 #ifndef MB_VAR_MINB
 #define MB_VAR_MINB 1
 #endif
+#define MB_NO_BDF   // no FBDF kernel for this model (compile time; the reference uses FBDF on its loop examples only)
 #include "mb_model_def.cuh"
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__

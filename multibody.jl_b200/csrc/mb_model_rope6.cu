@@ -1,4 +1,5 @@
 // Kernel set of model 'rope6' (C5, documented size: stiff 6-link rope, n = 42).
+#define MB_NO_BDF   // no FBDF kernel for this model (compile time; the reference uses FBDF on its loop examples only)
 #include "mb_model_def.cuh"
 #define MB_FN static __device__ __forceinline__
 #define MB_RESTRICT __restrict__

@@ -334,7 +334,7 @@ static int jit_model_load(const void* image, size_t len, mbb200_model** out) {
   if (rc) { delete m; return rc; }
   m->jit = new mbjit::Loaded;
   m->jit->mod.assign(g_dev.size(), nullptr);
-  for (int k = 0; k < 4; k++) m->jit->fn[k].assign(g_dev.size(), nullptr);
+  for (int k = 0; k < mbjit::NKERN; k++) m->jit->fn[k].assign(g_dev.size(), nullptr);
   rc = upload_tables(m);
   for (size_t i = 0; rc == MBB200_OK && i < g_dev.size(); i++) {
     cudaError_t ce = cudaSetDevice(g_dev[i]->ordinal);
@@ -342,7 +342,7 @@ static int jit_model_load(const void* image, size_t len, mbb200_model** out) {
     if (ce != cudaSuccess) { rc = fail(MBB200_ERR_CUDA, "device %d: %s", g_dev[i]->ordinal, cudaGetErrorString(ce)); break; }
     int dr = mbjit::g_api.ModuleLoadData(&m->jit->mod[i], cc.cubin.data());
     if (dr != 0) { rc = fail(MBB200_ERR_CUDA, "cuModuleLoadData failed (%d) for model '%s'", dr, im.name.c_str()); break; }
-    for (int k = 0; k < 4; k++)
+    for (int k = 0; k < mbjit::NKERN; k++)
       if (!cc.names[k].empty()) {
         dr = mbjit::g_api.ModuleGetFunction(&m->jit->fn[k][i], m->jit->mod[i], cc.names[k].c_str());
         if (dr != 0) { rc = fail(MBB200_ERR_CUDA, "kernel %s not found in the compiled image (%d)", cc.names[k].c_str(), dr); break; }
@@ -377,7 +377,7 @@ static void jit_unload(mbb200_model* m) {
 
 // same launch geometry as MB_DEFINE_MODEL (csrc/mb_model_def.cuh): 128-thread CTAs, persistent grid
 static cudaError_t jit_launch(const mbb200_model* m, int dev_index, int alg, const MbArgs& a, int sm_count, cudaStream_t st) {
-  void* fn = (alg >= 1 && alg <= 3) ? m->jit->fn[alg - 1][dev_index] : nullptr;
+  void* fn = (alg >= 1 && alg <= 3) ? m->jit->fn[alg - 1][dev_index] : (alg == 4 ? m->jit->fn[4][dev_index] : nullptr);
   if (!fn) return cudaErrorNotSupported;
   int bps = 1;
   if (mbjit::g_api.Occupancy(&bps, fn, 128, 0) != 0 || bps < 1) bps = 1;
@@ -562,7 +562,7 @@ extern "C" void mbb200_comm_destroy(void) {
 static int check_opts(const mbb200_model* m, const mbb200_opts* o, long long N, int n_save) {
   if (!m || !o) return fail(MBB200_ERR_BAD_ARG, "null model or options");
   if (g_dev.empty()) return fail(MBB200_ERR_NOT_INIT, "mbb200_init has not been called");
-  if (o->alg != MBB200_ALG_TSIT5 && o->alg != MBB200_ALG_RODAS5P && o->alg != MBB200_ALG_RODAS4) return fail(MBB200_ERR_BAD_ARG, "unknown algorithm id %d", o->alg);
+  if (o->alg != MBB200_ALG_TSIT5 && o->alg != MBB200_ALG_RODAS5P && o->alg != MBB200_ALG_RODAS4 && o->alg != MBB200_ALG_FBDF) return fail(MBB200_ERR_BAD_ARG, "unknown algorithm id %d", o->alg);
   if (o->alg == MBB200_ALG_TSIT5 && !m->entry->is_ode)
     return fail(MBB200_ERR_UNSUPPORTED, "Tsit5 needs an explicit ODE; model '%s' has a singular mass matrix (use Rodas5P or Rodas4)", m->entry->name);
   if (N < 0 || n_save < 0) return fail(MBB200_ERR_BAD_ARG, "negative size");
@@ -616,6 +616,8 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
   CU(cudaEventRecord(d.ev0, d.stream));
   if (Ns > 0) {
     cudaError_t e = m->jit ? jit_launch(m, dev_index, o->alg, a, d.sm_count, d.stream) : m->entry->launch(o->alg, a, d.sm_count, d.stream);
+    if (e != cudaSuccess && o->alg == MBB200_ALG_FBDF && (e == cudaErrorInvalidValue || e == cudaErrorNotSupported))
+      return fail(MBB200_ERR_UNSUPPORTED, "model '%s' has no FBDF kernel", m->entry->name);
     if (e != cudaSuccess) return fail(MBB200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
     d.last_launches++;
     if ((o->flags & MBB200_FLAG_REDUCE) && d_reduce && n_save > 0) {
@@ -731,6 +733,8 @@ extern "C" int mbb200_solve_device_static(mbb200_model* m, const mbb200_opts* o,
     cudaError_t e = m->jit ? jit_launch(m, dev_index, o->alg, a, d.sm_count, d.stream) : m->entry->launch(o->alg, a, d.sm_count, d.stream);
     if (e != cudaSuccess) {
       cudaStreamSynchronize(d.stream);
+      if (o->alg == MBB200_ALG_FBDF && (e == cudaErrorInvalidValue || e == cudaErrorNotSupported))
+        return fail(MBB200_ERR_UNSUPPORTED, "model '%s' has no FBDF kernel", m->entry->name);
       return fail(MBB200_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(e));
     }
     d.last_launches++;

@@ -37,12 +37,13 @@ def test_load_time_compiled_model_matches_scipy_and_the_reference_assertions(tmp
     U, P = _ensemble(s, N)
     sv = np.array([0.5, 1.0, 2.0])
     ep = api.EnsembleProblem(api.ODEProblem(s, tspan=(0.0, 2.0)), u0_matrix=U, p_matrix=P)
-    for alg in (api.Tsit5(), api.Rodas5P(), api.Rodas4()):
+    for alg in (api.Tsit5(), api.Rodas5P(), api.Rodas4(), api.FBDF()):
         sol = api.solve(ep, alg, api.EnsembleB200(), trajectories=N, saveat=sv, abstol=1e-9, reltol=1e-9)
         assert np.all(sol.retcode == 1)
+        bound = 2e-5 if isinstance(alg, api.FBDF) else 2e-7            # a BDF's global error sits further above its tolerance
         for j in (0, 17, 95):
             ref = solve_ivp(lambda t, u: s.eval_rhs(u, P[:, j], t), (0.0, 2.0), U[:, j], method="DOP853", rtol=1e-11, atol=1e-12, t_eval=sv)
-            assert np.abs(sol.u[:, :, j] - ref.y.T).max() < 2e-7, (type(alg).__name__, j)
+            assert np.abs(sol.u[:, :, j] - ref.y.T).max() < bound, (type(alg).__name__, j)
     # the reference's own run: Rodas4, default tolerances, (0, 35); rev1.phi -> -pi/2, body2.r_0[2] -> -2 (rtol 1e-2)
     ep35 = api.EnsembleProblem(api.ODEProblem(s, tspan=(0.0, 35.0)))
     sol = api.solve(ep35, api.Rodas4(), api.EnsembleB200(), trajectories=3, saveat=np.array([35.0]))

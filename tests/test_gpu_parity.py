@@ -17,7 +17,7 @@ def _run_gpu(spec, **kw):
     sys_ = api.multibody(spec.model)
     prob = api.ODEProblem(sys_, tspan=spec.tspan)
     eprob = api.EnsembleProblem(prob, u0_matrix=spec.u0, p_matrix=spec.p)
-    alg = {"tsit5": api.Tsit5(), "rodas5p": api.Rodas5P(), "rodas4": api.Rodas4()}[spec.alg]
+    alg = {"tsit5": api.Tsit5(), "rodas5p": api.Rodas5P(), "rodas4": api.Rodas4(), "fbdf": api.FBDF()}[spec.alg]
     return api.solve(eprob, alg, api.EnsembleB200(), trajectories=spec.u0.shape[1], saveat=spec.saveat,
                      abstol=spec.abstol, reltol=spec.reltol, **kw)
 
@@ -166,6 +166,45 @@ def test_rodas4_parity(oracle, config, N):
     spec = ensembles.make_ensemble(config, N)
     spec.alg = "rodas4"
     _compare(_run_gpu(spec), _run_oracle(oracle, spec))
+
+
+@pytest.mark.parametrize("config,N", [("C1", 512), ("C2B", 256), ("C3", 512), ("C3P", 512)])
+def test_fbdf_parity(oracle, config, N):
+    """FBDF (test/test_fourbar.jl:45,71; the variable-order BDF of csrc/mb_bdf.cuh) against the oracle's restatement of
+    the same formulation: ODEs and both loop DAEs.  Step and order decisions compare error norms with thresholds, so a
+    round-off difference (pivot order of the structured LU, device pow) can move a decision on a few trajectories:
+    by value every trajectory must stay within the integration tolerance (1e-8, scaled) x 100, the ensemble within
+    the north-star 1e-6, and the step counts within 2 %."""
+    spec = ensembles.make_ensemble(config, N)
+    spec.alg = "fbdf"
+    sol, ref = _run_gpu(spec), _run_oracle(oracle, spec)
+    assert np.array_equal(sol.retcode, ref["retcode"]) and np.all(sol.retcode == 1)
+    scale = np.maximum(np.abs(ref["u"]).max(axis=(0, 2), keepdims=True), 1e-3)
+    per_traj = (np.abs(sol.u - ref["u"]) / scale).max(axis=(0, 1))
+    same = (sol.stats[0] == ref["stats"][0]) & (sol.stats[1] == ref["stats"][1])
+    print(f"{config}: max err {per_traj.max():.2e}, median {np.median(per_traj):.2e}; identical step sequences on "
+          f"{same.mean() * 100:.1f} % of trajectories; naccept gpu {sol.stats[0].mean():.1f} oracle {ref['stats'][0].mean():.1f}")
+    assert per_traj.max() < RTOL
+    assert per_traj[same].max() < 1e-9 if same.any() else True       # same decisions -> same numbers to round-off
+    assert same.mean() > 0.5
+    assert abs(sol.stats[0].mean() - ref["stats"][0].mean()) <= 0.02 * ref["stats"][0].mean() + 2
+    np.testing.assert_allclose(sol.t_final, ref["t"], rtol=0, atol=1e-12)
+
+
+def test_fbdf_reference_call_site_and_unsupported_models(oracle):
+    """test/test_fourbar.jl:44-46 as written: FBDF on the four-bar, (0, 1.4399), successful return code; value checked
+    against Rodas5P at tight tolerance.  Models built without the kernel answer MBB200_ERR_UNSUPPORTED, never a silent
+    substitute."""
+    sys_ = api.multibody("fourbar")
+    ep = api.EnsembleProblem(api.ODEProblem(sys_, tspan=(0.0, 1.4399)))
+    a = api.solve(ep, api.FBDF(autodiff=True), api.EnsembleB200(), trajectories=4, saveat=np.array([0.7, 1.4399]))
+    b = api.solve(ep, api.Rodas5P(), api.EnsembleB200(), trajectories=4, saveat=np.array([0.7, 1.4399]), abstol=1e-11, reltol=1e-11)
+    assert np.all(a.retcode == 1) and np.all(b.retcode == 1)
+    assert np.abs(a.u - b.u).max() < 5e-3                              # default tolerances 1e-6 / 1e-3
+    spec = ensembles.make_ensemble("C4", 8)
+    eprob = api.EnsembleProblem(api.ODEProblem(api.multibody(spec.model), tspan=spec.tspan), u0_matrix=spec.u0, p_matrix=spec.p)
+    with pytest.raises(RuntimeError, match="no FBDF kernel"):
+        api.solve(eprob, api.FBDF(), api.EnsembleB200(), trajectories=8, saveat=spec.saveat)
 
 
 def test_dae_initialisation_on_device_matches_oracle(oracle):

@@ -94,7 +94,7 @@ def test_nvrtc_compiles_the_image_and_caches_the_cubin(cache):
     cubin = (cache / "cache" / files[0]).read_bytes()
     assert cubin[:4] == b"\x7fELF" and len(cubin) > 10000
     names = (cache / "cache" / files[1]).read_text().split()
-    assert len(names) == 4 and all("MbModel_jit" in x for x in names)       # Tsit5, Rodas5P, Rodas4, observed
+    assert len(names) == 5 and all("MbModel_jit" in x for x in names)       # Tsit5, Rodas5P, Rodas4, observed, FBDF
     sass = subprocess.run(["cuobjdump", "-elf", str(cache / "cache" / files[0])], capture_output=True, text=True).stdout
     assert "sm_100" in sass or "EF_CUDA_SM100" in sass or re.search(r"arch\s*=\s*sm_100", sass) or True
     t0 = os.path.getmtime(cache / "cache" / files[0])
