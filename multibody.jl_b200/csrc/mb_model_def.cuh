@@ -77,7 +77,9 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
   kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);
 #endif
 
-#define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR)                                                        \
+#define MB_DEFINE_MODEL(X, BLOCK, MINB, UNR) MB_DEFINE_MODEL_S(X, BLOCK, MINB, UNR, nullptr)
+// SCRATCH: size_t (*)(int alg, long long N, int sm_count) or nullptr -- device scratch the kernels of this model need
+#define MB_DEFINE_MODEL_S(X, BLOCK, MINB, UNR, SCRATCH)                                               \
   struct MbModel_##X {                                                                              \
     static constexpr int N = MBM_##X##_N, NP = MBM_##X##_M, NLU = MBM_##X##_NLU,                    \
                          HAS_DT = MBM_##X##_HAS_DT, IS_ODE = MBM_##X##_IS_ODE,                      \
@@ -163,7 +165,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
                                        MBM_##X##_IS_ODE,                                            \
                                        {MBM_##X##_F_RHS, MBM_##X##_F_JAC, MBM_##X##_F_DT,           \
                                         MBM_##X##_F_FACTOR, MBM_##X##_F_SOLVE},                     \
-                                       mb_launch_##X, MBM_##X##_NOBS, mb_launch_obs_##X, nullptr};                                     \
+                                       mb_launch_##X, MBM_##X##_NOBS, mb_launch_obs_##X, nullptr, SCRATCH};                                     \
   namespace {                                                                                       \
   struct MbReg_##X {                                                                                \
     MbReg_##X() { mb_register_model(&mb_entry_##X); }                                               \

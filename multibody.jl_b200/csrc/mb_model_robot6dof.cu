@@ -26,7 +26,7 @@
 #define MB_R_BLOCK 256
 #endif
 #define MB_S_STRIDE MB_R_BLOCK
-#if MB_ROWS_SMEM == 4
+#if MB_ROWS_SMEM == 4 || MB_ROWS_SMEM == 5
 #define MB_LU_AT(k) LU[(k) * MB_S_STRIDE]
 #define MB_ROWS_NLU 152
 #endif
@@ -34,5 +34,17 @@
 #ifndef MB_R_MINB
 #define MB_R_MINB 1
 #endif
-#define MB_EXPAND(...) MB_DEFINE_MODEL(__VA_ARGS__)
-MB_EXPAND(robot6dof, MB_R_BLOCK, MB_R_MINB, MB_R_UNR)
+#if MB_ROWS_SMEM == 5
+// LU slots of the Rosenbrock kernels live in device scratch: [CTA][slot][thread]; one CTA per SM (147 KB of shared rows)
+static size_t mb_robot_scratch(int alg, long long N, int sm_count) {
+  if (alg != 2 && alg != 3) return 0;
+  long long grid = 1ll * sm_count, need = (N + MB_R_BLOCK - 1) / MB_R_BLOCK;
+  if (grid > need) grid = need;
+  return (size_t)grid * MB_R_BLOCK * MB_ROWS_NLU * sizeof(double);
+}
+#define MB_R_SCRATCH mb_robot_scratch
+#else
+#define MB_R_SCRATCH nullptr
+#endif
+#define MB_EXPAND(...) MB_DEFINE_MODEL_S(__VA_ARGS__)
+MB_EXPAND(robot6dof, MB_R_BLOCK, MB_R_MINB, MB_R_UNR, MB_R_SCRATCH)

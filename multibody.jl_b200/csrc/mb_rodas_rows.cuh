@@ -28,7 +28,9 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   constexpr int N = M::N, NST = T::NST;
   constexpr double BETA1 = 7.0 / (10.0 * T::ORDER), BETA2 = 2.0 / (5.0 * T::ORDER);
   constexpr int NPR = (M::NP + N - 1) / N > 0 ? (M::NP + N - 1) / N : 1;
-  constexpr int NLUR = (M::NLU + N - 1) / N > 0 ? (M::NLU + N - 1) / N : 1;
+  constexpr bool SLU = MB_ROWS_SMEM == 4;   // mode 4: LU slots in shared memory
+  constexpr bool GLU = MB_ROWS_SMEM == 5;   // mode 5: LU slots in a global scratch ([slot][thread] per CTA) kept in the L2 set-aside
+  constexpr int NLUR = (SLU || GLU) ? 0 : ((M::NLU + N - 1) / N > 0 ? (M::NLU + N - 1) / N : 1);
   constexpr int R_US = NST, R_SC = NST + 1, R_U = NST + 2, R_DT = NST + 3, R_P = NST + 4, R_LU = R_P + NPR, ROWS = R_LU + NLUR;
   constexpr unsigned FULL = 0xffffffffu;
   constexpr double EPS = 2.220446049250313e-16;
@@ -39,12 +41,15 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const u = &W[R_U][0];
   double* const dT = &W[R_DT][0];
   double* const p = &W[R_P][0];
-  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2, SLU = MB_ROWS_SMEM == 4;   // mode 4: LU slots in shared memory too
+  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2;
   constexpr bool SDT = SROWS && MB_ROWS_SMEM != 3 && M::HAS_DT;            // mode 3: only the C-sum row
   constexpr int S_DT = N, S_US = (SDT ? 2 : 1) * N;     // shared rows: sc | df/dt (if any) | us (mode 2)
 #define MB_US(i) (*(SUS ? &srow[(size_t)(S_US + (i)) * BLOCK] : &us[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
-  double* const LU = SLU ? srow + (size_t)(2 * N) * BLOCK : &W[R_LU][0];   // mode 4: strided by MB_LU_AT (model TU)
+  // modes 4 / 5: slot k of this thread is LU[k * BLOCK] (MB_LU_AT of the model's translation unit)
+  double* const LU = SLU ? srow + (size_t)(2 * N) * BLOCK
+                   : GLU ? a.scratch + (size_t)blockIdx.x * ((size_t)M::NLU * BLOCK) + threadIdx.x
+                         : &W[0][0] + (size_t)R_LU * N;
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
   long long traj = -1, iter = 0;
   int is = 0, naccept = 0, nreject = 0, nf = 0, njac = 0, nsolve = 0;

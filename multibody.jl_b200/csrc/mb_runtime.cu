@@ -596,14 +596,14 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
   a.scratch = nullptr;
   if (m->entry->scratch_bytes && Ns > 0) {        // warp-per-trajectory kernels (long ropes): W, stage vectors, sweep scratch
     const size_t sb = m->entry->scratch_bytes(o->alg, Ns, d.sm_count);
-    if (d.ws2.bytes < sb) {
+    if (sb && d.ws2.bytes < sb) {
       CU(cudaStreamSynchronize(d.stream));
       if (d.ws2.ptr) CU(cudaFree(d.ws2.ptr));
       d.ws2.ptr = nullptr; d.ws2.bytes = 0;
       CU(cudaMalloc(&d.ws2.ptr, sb));
       d.ws2.bytes = sb;
     }
-    a.scratch = (double*)d.ws2.ptr;
+    a.scratch = sb ? (double*)d.ws2.ptr : nullptr;
   }
   d.last_launches = 0;
   CU(cudaMemsetAsync(d.queue, 0, sizeof(unsigned long long), d.stream));
