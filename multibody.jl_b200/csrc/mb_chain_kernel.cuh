@@ -180,7 +180,10 @@ __device__ __forceinline__ int chain_sv(int d) {
 }
 
 template <int NLINKS, int ELASTIC, class T, int BLOCK>
-__global__ void __launch_bounds__(BLOCK) chain_warp_kernel(const MbArgs a) {
+#ifndef MBC_MINB
+#define MBC_MINB 1      // tuning: minimum resident CTAs per SM the register allocation must allow
+#endif
+__global__ void __launch_bounds__(BLOCK, MBC_MINB) chain_warp_kernel(const MbArgs a) {
   using Dm = ChainDims<NLINKS, ELASTIC>;
   constexpr int N = Dm::N, NP = Dm::NP, NST = T::NST, M = Dm::M;
   __shared__ double sh_bq[BLOCK / 32][Dm::MPAD], sh_y[BLOCK / 32][Dm::MPAD], sh_di[BLOCK / 32][Dm::MPAD];

@@ -6,7 +6,7 @@ cd "$(dirname "$0")/../multibody.jl_b200/csrc"
 mkdir -p ../lib/variants
 for spec in "$@"; do
   name="${spec%%:*}"; flags="${spec#*:}"
-  ( make -s MODELS=robot6dof BUILD=build_$name LIB=../lib/variants/lib_$name.so EXTRA="$flags" 2>&1 | grep -v "deprecated-gpu-targets" || true ) &
+  ( make -s MODELS=${MODELS:-robot6dof} BUILD=build_$name LIB=../lib/variants/lib_$name.so EXTRA="$flags" 2>&1 | grep -v "deprecated-gpu-targets" || true ) &
 done
 wait
 ls -la ../lib/variants
