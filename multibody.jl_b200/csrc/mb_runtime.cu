@@ -604,6 +604,23 @@ static int enqueue_shard(Device& d, const mbb200_model* m, int dev_index, const 
       d.ws2.bytes = sb;
     }
     a.scratch = sb ? (double*)d.ws2.ptr : nullptr;
+    if (const char* pe = sb ? getenv("MBB200_L2_PERSIST") : nullptr) {   // tuning knob (off by default): pin the
+      int maxp = 0, maxw = 0;                                           // kernel scratch in the L2 set-aside, value = MB (<= 1: all)
+      cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, d.ordinal);
+      cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, d.ordinal);
+      size_t want = (size_t)atoll(pe) << 20;
+      if (want <= (1u << 20) || want > sb) want = sb;
+      const size_t setaside = want < (size_t)maxp ? want : (size_t)maxp;
+      CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setaside));
+      cudaStreamAttrValue v;
+      memset(&v, 0, sizeof(v));
+      v.accessPolicyWindow.base_ptr = d.ws2.ptr;
+      v.accessPolicyWindow.num_bytes = setaside < (size_t)maxw ? setaside : (size_t)maxw;
+      v.accessPolicyWindow.hitRatio = 1.0f;
+      v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+      v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+      CU(cudaStreamSetAttribute(d.stream, cudaStreamAttributeAccessPolicyWindow, &v));
+    }
   }
   d.last_launches = 0;
   CU(cudaMemsetAsync(d.queue, 0, sizeof(unsigned long long), d.stream));
