@@ -276,7 +276,13 @@ def main():
         chain = sys_.meta.get("chain")
         want = (f"chain_warp_kernel<{chain[0]}, {int(chain[1])}," if chain else f"MbModel_{spec.model},")
         tab = {"rodas5p": ("TabRodas5P", ", 2,"), "rodas4": ("TabRodas4", ", 3,"), "tsit5": (", 1,",), "fbdf": ("bdf_kernel",)}[spec.alg]
-        if tj and want in tj.get("kernel", "") and any(x in tj["kernel"] for x in tab):
+        # ... and the entry names the mangled symbol of the kernel it was captured on (template arguments = CTA size
+        # and row mode included): it must be present in the library this run loaded
+        sym_ok = True
+        if tj and tj.get("symbol"):
+            with open(_lib.LIB_PATH, "rb") as fh:
+                sym_ok = tj["symbol"].encode() in fh.read()
+        if tj and sym_ok and want in tj.get("kernel", "") and any(x in tj["kernel"] for x in tab):
             traffic = tj["dram_bytes_per_trajectory"] * N
             peak_hbm = 6530.6
             ppath = os.path.join(ROOT, "MEASURED_PEAKS.json")

@@ -270,8 +270,13 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append(pr.function(f"MB_FN void mbm_{X}_jac({args}, double* MB_RESTRICT Jnz)",
                            [(f"Jnz[{k}]", e[2]) for k, e in enumerate(code.jac_entries)]))
     out.append("")
+    # factor() and dT() read the state through MB_FU_AT so that a translation unit can keep it in shared memory, laid out
+    # [component][thread] (Rosenbrock row kernel, MB_ROWS_SMEM = 6)
+    out.append("#ifndef MB_FU_AT\n#define MB_FU_AT(i) u[i]\n#endif")
+    pr.input_fmt = dict(fmt, u="MB_FU_AT({i})")
     out.append(pr.function(f"MB_FN void mbm_{X}_dT({args}, double* MB_RESTRICT dT)",
                            [(f"dT[{i}]", code.dT_nodes[i]) for i in range(n)]))
+    pr.input_fmt = fmt
     out.append("")
     out.append(f"// observed variables, in this order: {', '.join(obs_names) if obs_names else '(none)'}")
     out.append(pr.function(f"MB_FN void mbm_{X}_observed({args}, double* MB_RESTRICT obs)",
@@ -280,8 +285,10 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     pr.smem_slots = slots if sys.meta.get("stage_factor", True) else 0
     out.append("#ifndef MB_LU_AT\n#define MB_LU_AT(k) LU[k]   /* slot k of this trajectory's LU storage (a TU may stride it) */\n#endif")
     lu_assign = [(f"MB_LU_AT({s})", node) for s, node in enumerate(code.lu_nodes)]
+    pr.input_fmt = dict(fmt, u="MB_FU_AT({i})")
     out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
+    pr.input_fmt = fmt
     out.append("")
     # runtime pivot guard: the pivot ORDER is fixed at code-generation time, so the code reports the largest stored
     # pivot reciprocal; the kernels retire a trajectory as Unstable when it is not finite or above MB_PIVOT_GUARD

@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #if MB_ROWS_SMEM == 4
 #define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((2 * (N) + MB_ROWS_NLU) * sizeof(double) * (BLOCK))
 #else
-#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((1 + (((HASDT) && MB_ROWS_SMEM != 3) ? 1 : 0) + (MB_ROWS_SMEM == 2 ? 1 : 0)) * (N) * sizeof(double) * (BLOCK))
+#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((1 + (((HASDT) && MB_ROWS_SMEM != 3) ? 1 : 0) + (MB_ROWS_SMEM == 2 ? 1 : 0) + (MB_ROWS_SMEM == 6 ? 2 : 0)) * (N) * sizeof(double) * (BLOCK))
 #endif
 #endif
 // rhs_s: right-hand side reading a [component][thread]-strided state (generated under MB_RHS_STRIDED)

@@ -1,8 +1,14 @@
 // Kernel set of model 'robot6dof' (generated/mbm_robot6dof.h is emitted by codegen/generate.py).
 #ifndef MB_ROWS_SMEM
-#define MB_ROWS_SMEM 1   // C-sum and df/dt rows in shared memory; 2 (stage state too) measured 3 % slower (profiles/r01_robot_v8_summary.md)
+// Rows of the Rosenbrock workspace kept in shared memory, [component][thread] (csrc/mb_rodas_rows.cuh):
+//   1  C-sum and df/dt                                  (round 1; 147 KB at 256 threads)
+//   6  C-sum, df/dt, stage state and state: 4 x 36 doubles per thread = 221 KB at 192 threads per CTA (shipped).
+// Throughput is flat between 192 and 256 threads per SM at equal thread-local traffic and rises as rows leave local
+// memory: 606 208 trajectories, same box: mode 1 x 256 threads 84.1k trajectories/s, mode 2 x 224 88.9k, mode 6 x 160
+// 89.7k, mode 6 x 192 95.8k (gpurun_out/var_thr2.log -> profiles/r02_robot_rows_modes.log).
+#define MB_ROWS_SMEM 6
 #endif
-#if MB_ROWS_SMEM == 2
+#if MB_ROWS_SMEM == 2 || MB_ROWS_SMEM == 6
 #define MB_RHS_STRIDED
 #endif
 #define MB_NO_BDF   // no FBDF kernel for this model (compile time; the reference uses FBDF on its loop examples only)
@@ -23,12 +29,15 @@
 #define MB_R_UNR 0
 #endif
 #ifndef MB_R_BLOCK
-#define MB_R_BLOCK 256
+#define MB_R_BLOCK 192
 #endif
 #define MB_S_STRIDE MB_R_BLOCK
 #if MB_ROWS_SMEM == 4 || MB_ROWS_SMEM == 5
 #define MB_LU_AT(k) LU[(k) * MB_S_STRIDE]
 #define MB_ROWS_NLU 152
+#endif
+#if MB_ROWS_SMEM == 6
+#define MB_FU_AT(i) u[(i) * MB_S_STRIDE]
 #endif
 #include "generated/mbm_robot6dof.h"
 #ifndef MB_R_MINB

@@ -41,10 +41,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   double* const u = &W[R_U][0];
   double* const dT = &W[R_DT][0];
   double* const p = &W[R_P][0];
-  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2;
+  constexpr bool SU = MB_ROWS_SMEM == 6;     // mode 6: mode 2 + the state row u (factor / dT read it through MB_FU_AT)
+  constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2 || SU;
   constexpr bool SDT = SROWS && MB_ROWS_SMEM != 3 && M::HAS_DT;            // mode 3: only the C-sum row
-  constexpr int S_DT = N, S_US = (SDT ? 2 : 1) * N;     // shared rows: sc | df/dt (if any) | us (mode 2)
+  constexpr int S_DT = N, S_US = (SDT ? 2 : 1) * N, S_U = S_US + N;     // shared rows: sc | df/dt (if any) | us (modes 2, 6) | u (mode 6)
 #define MB_US(i) (*(SUS ? &srow[(size_t)(S_US + (i)) * BLOCK] : &us[i]))
+#define MB_UU(i) (*(SU ? &srow[(size_t)(S_U + (i)) * BLOCK] : &u[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
   // modes 4 / 5: slot k of this thread is LU[k * BLOCK] (MB_LU_AT of the model's translation unit)
   double* const LU = SLU ? srow + (size_t)(2 * N) * BLOCK
@@ -90,6 +92,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
           dt = initial_dt<M>(*reinterpret_cast<const double(*)[N]>(u), p, tb, a.t0, dtmax, a.abstol, a.reltol, T::ORDER);
           nf += 2;
         }
+        if (SU) {
+#pragma unroll
+          for (int i = 0; i < N; i++) MB_UU(i) = u[i];
+        }
         active = true;
         if (!(t < a.t1)) rc = RC_SUCCESS;
         if (init_fail) rc = RC_INITIALFAILURE;
@@ -106,11 +112,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
       bool last = false;
       if (t + dt >= a.t1 - 100.0 * EPS * fabs(a.t1)) { dt = a.t1 - t; last = true; }
       const double cW = 1.0 / (dt * T::GAMMA);
-      M::factor(u, p, t, tb, cW, LU);
+      const double* const ust = SU ? srow + (size_t)S_U * BLOCK : u;      // the state as factor() / dT() address it
+      M::factor(ust, p, t, tb, cW, LU);
       const bool badpiv = !(M::pivmax(LU) <= MB_PIVOT_GUARD);     // statically ordered LU hit a numerically zero pivot
       njac++;
       if (M::HAS_DT) {
-        M::dT(u, p, t, tb, dT);
+        M::dT(ust, p, t, tb, dT);
         if (SDT) {
 #pragma unroll
           for (int i = 0; i < N; i++) srow[(size_t)(S_DT + i) * BLOCK] = dT[i];
@@ -122,7 +129,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         {
           double x[N], y[N];
 #pragma unroll
-          for (int i = 0; i < N; i++) { x[i] = u[i]; y[i] = 0.0; }
+          for (int i = 0; i < N; i++) { x[i] = MB_UU(i); y[i] = 0.0; }
 #pragma unroll 1
           for (int j = 0; j < s; j++) {
             const double aj = T::A(s, j), cj = T::C(s, j);
@@ -163,7 +170,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         double sacc = 0.0;
 #pragma unroll
         for (int i = 0; i < N; i++) {
-          const double k8 = W[NST - 1][i], ua = u[i], ub = MB_US(i) + k8;
+          const double k8 = W[NST - 1][i], ua = MB_UU(i), ub = MB_US(i) + k8;
           const double scl = a.abstol + fmax(fabs(ua), fabs(ub)) * a.reltol;
           const double q = k8 / scl;
           sacc += q * q;
@@ -201,13 +208,13 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
                   K1 = fma(T::H(0, j), kj, K1); K2 = fma(T::H(1, j), kj, K2); K3 = fma(T::H(2, j), kj, K3);
                 }
                 const double un = MB_US(i) + W[NST - 1][i];
-                o[(size_t)i * a.N] = (1.0 - th) * u[i] + th * (un + (1.0 - th) * (K1 + th * (K2 + th * K3)));
+                o[(size_t)i * a.N] = (1.0 - th) * MB_UU(i) + th * (un + (1.0 - th) * (K1 + th * (K2 + th * K3)));
               }
             }
             is++;
           }
 #pragma unroll
-          for (int i = 0; i < N; i++) u[i] = MB_US(i) + W[NST - 1][i];
+          for (int i = 0; i < N; i++) MB_UU(i) = MB_US(i) + W[NST - 1][i];
           t = tn;
           qold = fmax(EEst, QOLDINIT);
           if (a.qs_min <= q && q <= a.qs_max) q = 1.0;      // dead band of step_accept_controller!
@@ -234,5 +241,6 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 }
 
 #undef MB_US
+#undef MB_UU
 
 }  // namespace mbk
