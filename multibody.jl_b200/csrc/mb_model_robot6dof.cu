@@ -44,7 +44,7 @@
 #define MB_R_MINB 1
 #endif
 #if MB_ROWS_SMEM == 5
-// LU slots of the Rosenbrock kernels live in device scratch: [CTA][slot][thread]; one CTA per SM (147 KB of shared rows)
+// LU slots of the Rosenbrock kernels live in device scratch: [CTA][slot][thread]; one CTA per SM
 static size_t mb_robot_scratch(int alg, long long N, int sm_count) {
   if (alg != 2 && alg != 3) return 0;
   long long grid = 1ll * sm_count, need = (N + MB_R_BLOCK - 1) / MB_R_BLOCK;

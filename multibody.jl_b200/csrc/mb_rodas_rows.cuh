@@ -9,16 +9,24 @@
 // 216 of the 255 registers) were live in registers across the inlined rhs(), which left its
 // 2 400-flop body ~40 registers: 300 LDL + 155 STL of spill code, executed 8 times per step.
 //
-// MB_ROWS_SMEM = 1 (set by the model's translation unit) moves the two rows that are written once
-// and read back per stage or per step -- the C-sum `sc` and df/dt -- from local memory to shared
-// memory, laid out [component][thread] (conflict-free): 2 N doubles per thread (147 KB for the
-// robot's 256-thread CTA), ~20 % of the step's thread-local DRAM traffic.  MB_ROWS_SMEM = 2 also
-// keeps the stage state `us` there; the model then provides rhs_s(), a copy of the right-hand
-// side that reads its state with the [component][thread] stride (MB_RHS_STRIDED).
+// MB_ROWS_SMEM (set by the model's translation unit) moves rows from local memory to shared memory, laid out
+// [component][thread] (conflict-free):
+//   1  the C-sum `sc` and df/dt, the two rows written once and read back per stage or per step
+//   2  + the stage state `us`; the model then provides rhs_s(), a copy of the right-hand side that reads its state with
+//      the [component][thread] stride (MB_RHS_STRIDED)
+//   3  only the C-sum          4  mode 1 + the LU slots          5  mode 1, LU slots in a global scratch (a.scratch)
+//   6  mode 2 + the state `u` (factor() / dT() read it through MB_FU_AT): 4 N doubles per thread, 221 KB for the robot's
+//      192-thread CTA -- the shipped robot configuration (numbers: csrc/mb_model_robot6dof.cu)
 #pragma once
 #include "mb_ensemble.cuh"
 #ifndef MB_ROWS_SMEM
 #define MB_ROWS_SMEM 0
+#endif
+#ifndef MB_ROWS_JSPLIT
+#define MB_ROWS_JSPLIT 1     // slices of the component range in the stage-combination loop (must divide N)
+#endif
+#ifndef MB_ROWS_JUNROLL
+#define MB_ROWS_JUNROLL 1    // rows of k in flight per slice
 #endif
 
 namespace mbk {
@@ -32,8 +40,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   constexpr bool GLU = MB_ROWS_SMEM == 5;   // mode 5: LU slots in a global scratch ([slot][thread] per CTA) kept in the L2 set-aside
   constexpr int NLUR = (SLU || GLU) ? 0 : ((M::NLU + N - 1) / N > 0 ? (M::NLU + N - 1) / N : 1);
   constexpr int R_US = NST, R_SC = NST + 1, R_U = NST + 2, R_DT = NST + 3, R_P = NST + 4, R_LU = R_P + NPR, ROWS = R_LU + NLUR;
-  constexpr unsigned FULL = 0xffffffffu;
   constexpr double EPS = 2.220446049250313e-16;
+  constexpr int NH = (N % MB_ROWS_JSPLIT == 0) ? MB_ROWS_JSPLIT : 1, HN = N / NH, JUN = MB_ROWS_JUNROLL;
 
   double W[ROWS][N];
   double* const us = &W[R_US][0];
@@ -124,14 +132,21 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         }
       }
       const double inv_dt = 1.0 / dt;
-#pragma unroll 1
-      for (int s = 0; s < NST; s++) {
-        {
-          double x[N], y[N];
+#ifdef MB_ROWS_CARRY
+      // Variant (set by the model's translation unit): the accumulators of the NEXT stage are carried across the loop, so the
+      // newest row k_s enters them from registers and the loop over stored rows stops at k_{s-2} (7 of the 28 row reads of a
+      // Rodas5P step gone); the right-hand side hands its output over in registers; the last stage accumulates the error
+      // norm from registers and leaves u_new = us + k_NST in the stage-state row.
+      double EEst;
+      {
+        double x[N], y[N];
+        double sacc = 0.0;
 #pragma unroll
-          for (int i = 0; i < N; i++) { x[i] = MB_UU(i); y[i] = 0.0; }
+        for (int i = 0; i < N; i++) { x[i] = MB_UU(i); y[i] = 0.0; }
 #pragma unroll 1
-          for (int j = 0; j < s; j++) {
+        for (int s = 0; s < NST; s++) {
+#pragma unroll 1
+          for (int j = 0; j + 1 < s; j++) {
             const double aj = T::A(s, j), cj = T::C(s, j);
 #pragma unroll
             for (int i = 0; i < N; i++) {
@@ -145,7 +160,84 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             MB_US(i) = x[i];
             if (SROWS) srow[(size_t)i * BLOCK] = y[i]; else sc[i] = y[i];
           }
+          double r[N];
+          if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, r);
+          else M::rhs(us, p, t + T::CT(s) * dt, tb, r);
+          const double dd = dt * T::D(s);
+#pragma unroll
+          for (int i = 0; i < N; i++) {
+            double v = r[i];
+            if (M::HAS_DT) v = fma(dd, SDT ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
+            if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
+            r[i] = v;
+          }
+          M::solve(LU, cW, p, r);
+#pragma unroll
+          for (int i = 0; i < N; i++) W[s][i] = r[i];
+          {   // unconditional (the last stage writes values nobody reads): x, y must be dead across the right-hand side
+            const int sn = s + 1 < NST ? s + 1 : s;
+            const double a1 = T::A(sn, s), c1 = T::C(sn, s);
+#pragma unroll
+            for (int i = 0; i < N; i++) { x[i] = fma(a1, r[i], MB_UU(i)); y[i] = c1 * r[i]; }
+          }
+          if (s + 1 == NST) {
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+              const double k8 = r[i], ua = MB_UU(i), ub = MB_US(i) + k8;
+              MB_US(i) = ub;
+              const double scl = a.abstol + fmax(fabs(ua), fabs(ub)) * a.reltol;
+              const double q = k8 / scl;
+              sacc += q * q;
+            }
+          }
         }
+        EEst = sqrt(sacc / N);
+      }
+      nf += NST; nsolve += NST;
+#define MB_UN(i) MB_US(i)
+#else
+#pragma unroll 1
+      for (int s = 0; s < NST; s++) {
+        // stage state us = u + sum_j A[s][j] k_j and C-sum sc = sum_j C[s][j] k_j.  The components are processed in
+        // MB_ROWS_JSPLIT slices so that MB_ROWS_JUNROLL rows of k can be in flight at once (registers: 2 slice
+        // accumulators + JUNROLL slices of a row): fewer exposed round trips to thread-local memory per stage
+#pragma unroll 1
+        for (int h = 0; h < NH; h++) {
+          const int i0 = h * HN;
+          double x[HN], y[HN];
+#pragma unroll
+          for (int i = 0; i < HN; i++) { x[i] = MB_UU(i0 + i); y[i] = 0.0; }
+#pragma unroll(JUN)
+          for (int j = 0; j < s; j++) {
+            const double aj = T::A(s, j), cj = T::C(s, j);
+#pragma unroll
+            for (int i = 0; i < HN; i++) {
+              const double kj = W[j][i0 + i];
+              x[i] = fma(aj, kj, x[i]);
+              y[i] = fma(cj, kj, y[i]);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < HN; i++) {
+            MB_US(i0 + i) = x[i];
+            if (SROWS) srow[(size_t)(i0 + i) * BLOCK] = y[i]; else sc[i0 + i] = y[i];
+          }
+        }
+#ifdef MB_ROWS_RHS_REG
+        // variant: the right-hand side hands its output over in registers instead of through the row k[s]
+        {
+          double r[N];
+          if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, r);
+          else M::rhs(us, p, t + T::CT(s) * dt, tb, r);
+          const double dd = dt * T::D(s);
+#pragma unroll
+          for (int i = 0; i < N; i++) {
+            double v = r[i];
+            if (M::HAS_DT) v = fma(dd, SDT ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
+            if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
+            r[i] = v;
+          }
+#else
         if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, &W[s][0]);
         else M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
         {
@@ -158,6 +250,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
+#endif
           M::solve(LU, cW, p, r);
 #pragma unroll
           for (int i = 0; i < N; i++) W[s][i] = r[i];
@@ -177,6 +270,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         }
         EEst = sqrt(sacc / N);
       }
+#define MB_UN(i) (MB_US(i) + W[NST - 1][i])
+#endif
       if (badpiv) {
         rc = RC_UNSTABLE;
       } else if (!isfinite(EEst)) {
@@ -197,7 +292,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             double* __restrict__ o = a.out_u + (size_t)is * N * a.N + traj;
             if (ts == tn) {
 #pragma unroll
-              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = MB_US(i) + W[NST - 1][i];
+              for (int i = 0; i < N; i++) o[(size_t)i * a.N] = MB_UN(i);
             } else {
               const double th = (ts - t) / dt;
               for (int i = 0; i < N; i++) {
@@ -207,14 +302,14 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
                   const double kj = W[j][i];
                   K1 = fma(T::H(0, j), kj, K1); K2 = fma(T::H(1, j), kj, K2); K3 = fma(T::H(2, j), kj, K3);
                 }
-                const double un = MB_US(i) + W[NST - 1][i];
+                const double un = MB_UN(i);
                 o[(size_t)i * a.N] = (1.0 - th) * MB_UU(i) + th * (un + (1.0 - th) * (K1 + th * (K2 + th * K3)));
               }
             }
             is++;
           }
 #pragma unroll
-          for (int i = 0; i < N; i++) MB_UU(i) = MB_US(i) + W[NST - 1][i];
+          for (int i = 0; i < N; i++) MB_UU(i) = MB_UN(i);
           t = tn;
           qold = fmax(EEst, QOLDINIT);
           if (a.qs_min <= q && q <= a.qs_max) q = 1.0;      // dead band of step_accept_controller!
@@ -242,5 +337,6 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 
 #undef MB_US
 #undef MB_UU
+#undef MB_UN
 
 }  // namespace mbk
