@@ -233,6 +233,9 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     slots = int(sys.meta.get("smem_slots", 0))
     out.append(f"#define MBM_{X}_SMEM_SLOTS {slots}")
     out.append(f"#define MBM_{X}_HAS_DT {1 if any(d != g.zero for d in code.dT_nodes) else 0}")
+    # rows of df/dt that are not structurally zero (bit i; all ones when n > 64): the Rosenbrock row kernel keeps only those
+    dt_mask = sum(1 << i for i, d in enumerate(code.dT_nodes) if d != g.zero) if n <= 64 else (1 << 64) - 1
+    out.append(f"#define MBM_{X}_DT_MASK 0x{dt_mask:x}ull")
     out.append(f"#define MBM_{X}_IS_ODE {1 if all(sys.mass_diag) else 0}")
     out.append("#ifndef MB_NO_PATTERN")
     out.append(_carray("int", f"mbm_{X}_jrow", [e[0] for e in code.jac_entries]))

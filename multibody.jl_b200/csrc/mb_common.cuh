@@ -57,6 +57,7 @@ __device__ __forceinline__ double mb_tab(const MbSeg& sg, int table) {
 #define MB_SINCOS(x, s, c) sincos(x, &(s), &(c))
 // staged temporaries of the generated code (codegen/emit.py): slot k of this thread, in dynamic
 // shared memory laid out [slot][thread] (conflict-free); MB_S_STRIDE = threads per CTA of the TU
+__host__ __device__ constexpr int mb_popc64(unsigned long long m) { int c = 0; for (; m; m &= m - 1) c++; return c; }
 extern __shared__ double mb_dyn_smem[];
 #define MB_S_DECL
 #define MB_S(k) ((volatile double*)mb_dyn_smem)[(k) * MB_S_STRIDE + threadIdx.x]   // volatile: no store-to-load forwarding back into registers

@@ -61,13 +61,17 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
   mbk::rosenbrock_rows_kernel<MODEL, typename mbk::TabOf<ALG>::type, BLOCK, MINB>
 #endif
 
+#ifndef MB_ROWS_LU_SMEM
+#define MB_ROWS_LU_SMEM 0      // LU slots 0 .. MB_ROWS_LU_SMEM-1 live in shared memory (the model's MB_LU_AT must agree)
+#endif
 #if defined(MB_RODAS_CLASSIC) || !MB_ROWS_SMEM
-#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) 0
+#define MB_ROWS_SMEM_BYTES_M(N, HASDT, BLOCK, MASK) 0
 #else
 #if MB_ROWS_SMEM == 4
-#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((2 * (N) + MB_ROWS_NLU) * sizeof(double) * (BLOCK))
+#define MB_ROWS_SMEM_BYTES_M(N, HASDT, BLOCK, MASK) (((N) + ((HASDT) ? mb_popc64(MASK) : 0) + MB_ROWS_NLU) * sizeof(double) * (BLOCK))
 #else
-#define MB_ROWS_SMEM_BYTES(N, HASDT, BLOCK) ((1 + (((HASDT) && MB_ROWS_SMEM != 3) ? 1 : 0) + (MB_ROWS_SMEM == 2 ? 1 : 0) + (MB_ROWS_SMEM == 6 ? 2 : 0)) * (N) * sizeof(double) * (BLOCK))
+// rows: C-sum (N) | df/dt (its structurally non-zero entries, not in mode 3) | stage state (modes 2, 6) | state (mode 6) | LU slots (MB_ROWS_LU_SMEM)
+#define MB_ROWS_SMEM_BYTES_M(N, HASDT, BLOCK, MASK) (((1 + (MB_ROWS_SMEM == 2 ? 1 : 0) + (MB_ROWS_SMEM == 6 ? 2 : 0)) * (N) + (((HASDT) && MB_ROWS_SMEM != 3) ? mb_popc64(MASK) : 0) + MB_ROWS_LU_SMEM) * sizeof(double) * (BLOCK))
 #endif
 #endif
 // rhs_s: right-hand side reading a [component][thread]-strided state (generated under MB_RHS_STRIDED)
@@ -102,6 +106,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
     static constexpr int N = MBM_##X##_N, NP = MBM_##X##_M, NLU = MBM_##X##_NLU,                    \
                          HAS_DT = MBM_##X##_HAS_DT, IS_ODE = MBM_##X##_IS_ODE,                      \
                          SLOTS = MBM_##X##_SMEM_SLOTS;                                              \
+    static constexpr unsigned long long DT_MASK = MBM_##X##_DT_MASK;                                \
     static __device__ __forceinline__ void rhs(const double* u, const double* p, double t,         \
                                                const double* tb, double* du) {                      \
       mbm_##X##_rhs(u, p, t, tb, du);                                                               \
@@ -144,7 +149,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, BLOCK, smem, st>>>(a);                                                    \
     } else if (alg == 2) {                                                                          \
-      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, MBM_##X##_HAS_DT, BLOCK);                                \
+      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES_M(MBM_##X##_N, MBM_##X##_HAS_DT, BLOCK, MBM_##X##_DT_MASK);                                \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, 2, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \
@@ -156,7 +161,7 @@ static inline int mb_carveout(size_t smem) { return smem ? (int)((smem * 100 + 2
       if (grid > need) grid = need;                                                                 \
       kern<<<(unsigned)grid, bt, smem, st>>>(a);                                                    \
     } else if (alg == 3) {                                                                          \
-      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES(MBM_##X##_N, MBM_##X##_HAS_DT, BLOCK);                                \
+      smem = smem0 + (size_t)MB_ROWS_SMEM_BYTES_M(MBM_##X##_N, MBM_##X##_HAS_DT, BLOCK, MBM_##X##_DT_MASK);                                \
       auto kern = MB_RODAS_KERNEL(MbModel_##X, 3, BLOCK, MINB, UNR);                                   \
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
       cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, mb_carveout(smem)); \

@@ -35,6 +35,10 @@
 #if MB_ROWS_SMEM == 4 || MB_ROWS_SMEM == 5
 #define MB_LU_AT(k) LU[(k) * MB_S_STRIDE]
 #define MB_ROWS_NLU 152
+#elif defined(MB_ROWS_LU_SMEM) && MB_ROWS_LU_SMEM > 0
+// the first MB_ROWS_LU_SMEM LU slots live in the shared rows behind sc (36) | df/dt (12 non-zero) | us (36) | u (36)
+#define MB_ROWS_LUS0 120
+#define MB_LU_AT(k) (*((k) < MB_ROWS_LU_SMEM ? (mb_dyn_smem + (size_t)(MB_ROWS_LUS0 + (k)) * MB_S_STRIDE + threadIdx.x) : (LU + (k))))
 #endif
 #if MB_ROWS_SMEM == 6
 #define MB_FU_AT(i) u[(i) * MB_S_STRIDE]

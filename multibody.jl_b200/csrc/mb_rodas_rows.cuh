@@ -22,6 +22,9 @@
 #ifndef MB_ROWS_SMEM
 #define MB_ROWS_SMEM 0
 #endif
+#if !defined(MB_ROWS_NO_CARRY) && !defined(MB_ROWS_CARRY)
+#define MB_ROWS_CARRY        // carried stage accumulators (below); MB_ROWS_NO_CARRY selects the first formulation
+#endif
 #ifndef MB_ROWS_JSPLIT
 #define MB_ROWS_JSPLIT 1     // slices of the component range in the stage-combination loop (must divide N)
 #endif
@@ -52,12 +55,21 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   constexpr bool SU = MB_ROWS_SMEM == 6;     // mode 6: mode 2 + the state row u (factor / dT read it through MB_FU_AT)
   constexpr bool SROWS = MB_ROWS_SMEM != 0, SUS = MB_ROWS_SMEM == 2 || SU;
   constexpr bool SDT = SROWS && MB_ROWS_SMEM != 3 && M::HAS_DT;            // mode 3: only the C-sum row
-  constexpr int S_DT = N, S_US = (SDT ? 2 : 1) * N, S_U = S_US + N;     // shared rows: sc | df/dt (if any) | us (modes 2, 6) | u (mode 6)
+  // shared rows: sc | df/dt (its structurally non-zero entries only) | us (modes 2, 6) | u (mode 6) | LU slots (mode 4: all;
+  // otherwise the first MB_ROWS_LU_SMEM, addressed by the model's MB_LU_AT)
+  constexpr unsigned long long DTM = M::DT_MASK & (N >= 64 ? ~0ull : ((1ull << (N & 63)) - 1ull));
+  constexpr int NDTS = SDT ? mb_popc64(DTM) : 0;
+  constexpr int S_DT = N, S_US = N + NDTS, S_U = S_US + (SUS ? N : 0), S_LUS = S_U + (SU ? N : 0);
+#ifdef MB_ROWS_LUS0
+  static_assert(MB_ROWS_LU_SMEM == 0 || S_LUS == MB_ROWS_LUS0, "MB_LU_AT of the model and the row layout disagree");
+#endif
+#define MB_DTNZ(i) (((DTM >> ((i) & 63)) & 1ull) != 0ull)
+#define MB_DTS(i) (S_DT + mb_popc64(DTM & ((1ull << ((i) & 63)) - 1ull)))
 #define MB_US(i) (*(SUS ? &srow[(size_t)(S_US + (i)) * BLOCK] : &us[i]))
 #define MB_UU(i) (*(SU ? &srow[(size_t)(S_U + (i)) * BLOCK] : &u[i]))
   double* const srow = mb_dyn_smem + (size_t)M::SLOTS * BLOCK + threadIdx.x;   // [row][component][thread]
   // modes 4 / 5: slot k of this thread is LU[k * BLOCK] (MB_LU_AT of the model's translation unit)
-  double* const LU = SLU ? srow + (size_t)(2 * N) * BLOCK
+  double* const LU = SLU ? srow + (size_t)S_LUS * BLOCK
                    : GLU ? a.scratch + (size_t)blockIdx.x * ((size_t)M::NLU * BLOCK) + threadIdx.x
                          : &W[0][0] + (size_t)R_LU * N;
   double t = 0.0, dt = 0.0, qold = QOLDINIT;
@@ -128,12 +140,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         M::dT(ust, p, t, tb, dT);
         if (SDT) {
 #pragma unroll
-          for (int i = 0; i < N; i++) srow[(size_t)(S_DT + i) * BLOCK] = dT[i];
+          for (int i = 0; i < N; i++) if (MB_DTNZ(i)) srow[(size_t)MB_DTS(i) * BLOCK] = dT[i];
         }
       }
       const double inv_dt = 1.0 / dt;
 #ifdef MB_ROWS_CARRY
-      // Variant (set by the model's translation unit): the accumulators of the NEXT stage are carried across the loop, so the
+      // The accumulators of the NEXT stage are carried across the loop, so the
       // newest row k_s enters them from registers and the loop over stored rows stops at k_{s-2} (7 of the 28 row reads of a
       // Rodas5P step gone); the right-hand side hands its output over in registers; the last stage accumulates the error
       // norm from registers and leaves u_new = us + k_NST in the stage-state row.
@@ -167,7 +179,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = r[i];
-            if (M::HAS_DT) v = fma(dd, SDT ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
+            if (M::HAS_DT && MB_DTNZ(i)) v = fma(dd, SDT ? srow[(size_t)MB_DTS(i) * BLOCK] : dT[i], v);
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
@@ -233,7 +245,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = r[i];
-            if (M::HAS_DT) v = fma(dd, SDT ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
+            if (M::HAS_DT && MB_DTNZ(i)) v = fma(dd, SDT ? srow[(size_t)MB_DTS(i) * BLOCK] : dT[i], v);
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
@@ -246,7 +258,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) {
             double v = W[s][i];
-            if (M::HAS_DT) v = fma(dd, SDT ? srow[(size_t)(S_DT + i) * BLOCK] : dT[i], v);
+            if (M::HAS_DT && MB_DTNZ(i)) v = fma(dd, SDT ? srow[(size_t)MB_DTS(i) * BLOCK] : dT[i], v);
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
@@ -336,6 +348,8 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 }
 
 #undef MB_US
+#undef MB_DTNZ
+#undef MB_DTS
 #undef MB_UU
 #undef MB_UN
 
