@@ -261,7 +261,8 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
         # second copy of the right-hand side reading its state from shared memory laid out
         # [component][thread] (u points at this thread's column): the stage state of the
         # Rosenbrock row kernel (csrc/mb_rodas_rows.cuh, MB_ROWS_SMEM = 2)
-        pr.input_fmt = dict(fmt, u="u[{i} * MB_S_STRIDE]")
+        pr.input_fmt = dict(fmt, u="u[{i} * MB_S_STRIDE]", p="MB_FP_AT({i})")
+        out.append("#ifndef MB_FP_AT\n#define MB_FP_AT(i) p[i]   /* parameters as rhs_s / factor / dT / solve read them (a TU may keep them in shared memory) */\n#endif")
         out.append("#ifdef MB_RHS_STRIDED")
         out.append(pr.function(f"MB_FN_RHS void mbm_{X}_rhs_s(const double* u, const double* MB_RESTRICT p, double t, "
                                f"const double* MB_RESTRICT tb, double* MB_RESTRICT du)",
@@ -276,7 +277,8 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     # factor() and dT() read the state through MB_FU_AT so that a translation unit can keep it in shared memory, laid out
     # [component][thread] (Rosenbrock row kernel, MB_ROWS_SMEM = 6)
     out.append("#ifndef MB_FU_AT\n#define MB_FU_AT(i) u[i]\n#endif")
-    pr.input_fmt = dict(fmt, u="MB_FU_AT({i})")
+    out.append("#ifndef MB_FP_AT\n#define MB_FP_AT(i) p[i]\n#endif")
+    pr.input_fmt = dict(fmt, u="MB_FU_AT({i})", p="MB_FP_AT({i})")
     out.append(pr.function(f"MB_FN void mbm_{X}_dT({args}, double* MB_RESTRICT dT)",
                            [(f"dT[{i}]", code.dT_nodes[i]) for i in range(n)]))
     pr.input_fmt = fmt
@@ -288,7 +290,7 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     pr.smem_slots = slots if sys.meta.get("stage_factor", True) else 0
     out.append("#ifndef MB_LU_AT\n#define MB_LU_AT(k) LU[k]   /* slot k of this trajectory's LU storage (a TU may stride it) */\n#endif")
     lu_assign = [(f"MB_LU_AT({s})", node) for s, node in enumerate(code.lu_nodes)]
-    pr.input_fmt = dict(fmt, u="MB_FU_AT({i})")
+    pr.input_fmt = dict(fmt, u="MB_FU_AT({i})", p="MB_FP_AT({i})")
     out.append(pr.function(f"MB_FN_FACTOR void mbm_{X}_factor({args}, double c, double* MB_RESTRICT LU)",
                            lu_assign))
     pr.input_fmt = fmt
@@ -305,7 +307,7 @@ def emit_model_header(sys, code: Optional[ModelCode] = None) -> str:
     out.append("\n".join(pl))
     out.append("")
     pr.smem_slots = 0
-    spr = Printer(code.solve_graph, {"lu": "MB_LU_AT({i})", "b": "b{i}", "c": "c", "p": "p[{i}]"})
+    spr = Printer(code.solve_graph, {"lu": "MB_LU_AT({i})", "b": "b{i}", "c": "c", "p": "MB_FP_AT({i})"})
     sol_lines = [f"MB_FN_SOLVE void mbm_{X}_solve(const double* MB_RESTRICT LU, double c, const double* MB_RESTRICT p, "
                  f"double* MB_RESTRICT b) {{"]
     for i in range(n):

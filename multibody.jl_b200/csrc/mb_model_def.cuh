@@ -71,7 +71,7 @@ __global__ void __launch_bounds__(256) mb_observed_kernel(const MbObsArgs a) {
 #define MB_ROWS_SMEM_BYTES_M(N, HASDT, BLOCK, MASK) (((N) + ((HASDT) ? mb_popc64(MASK) : 0) + MB_ROWS_NLU) * sizeof(double) * (BLOCK))
 #else
 // rows: C-sum (N) | df/dt (its structurally non-zero entries, not in mode 3) | stage state (modes 2, 6) | state (mode 6) | LU slots (MB_ROWS_LU_SMEM)
-#define MB_ROWS_SMEM_BYTES_M(N, HASDT, BLOCK, MASK) (((1 + (MB_ROWS_SMEM == 2 ? 1 : 0) + (MB_ROWS_SMEM == 6 ? 2 : 0)) * (N) + (((HASDT) && MB_ROWS_SMEM != 3) ? mb_popc64(MASK) : 0) + MB_ROWS_LU_SMEM) * sizeof(double) * (BLOCK))
+#define MB_ROWS_SMEM_BYTES_M(N, HASDT, BLOCK, MASK) (((1 + (MB_ROWS_SMEM == 2 ? 1 : 0) + (MB_ROWS_SMEM == 6 ? 2 : 0)) * (N) + (((HASDT) && MB_ROWS_SMEM != 3) ? mb_popc64(MASK) : 0) + MB_ROWS_LU_SMEM + MB_ROWS_P_SMEM) * sizeof(double) * (BLOCK))
 #endif
 #endif
 // rhs_s: right-hand side reading a [component][thread]-strided state (generated under MB_RHS_STRIDED)

@@ -2,11 +2,15 @@
 #ifndef MB_ROWS_SMEM
 // Rows of the Rosenbrock workspace kept in shared memory, [component][thread] (csrc/mb_rodas_rows.cuh):
 //   1  C-sum and df/dt                                  (round 1; 147 KB at 256 threads)
-//   6  C-sum, df/dt, stage state and state: 4 x 36 doubles per thread = 221 KB at 192 threads per CTA (shipped).
+//   6  C-sum, df/dt (its 12 non-zero entries), stage state, state and the 19 parameters: 139 doubles per thread = 214 KB
+//      at 192 threads per CTA (shipped).
 // Throughput is flat between 192 and 256 threads per SM at equal thread-local traffic and rises as rows leave local
 // memory: 606 208 trajectories, same box: mode 1 x 256 threads 84.1k trajectories/s, mode 2 x 224 88.9k, mode 6 x 160
 // 89.7k, mode 6 x 192 95.8k (gpurun_out/var_thr2.log -> profiles/r02_robot_rows_modes.log).
 #define MB_ROWS_SMEM 6
+#endif
+#if MB_ROWS_SMEM == 6 && !defined(MB_ROWS_P_SMEM)
+#define MB_ROWS_P_SMEM 19   // the 19 swept parameters in shared memory as well (read by every rhs / factor / dT / solve): +1.8 %
 #endif
 #if MB_ROWS_SMEM == 2 || MB_ROWS_SMEM == 6
 #define MB_RHS_STRIDED
@@ -42,6 +46,9 @@
 #endif
 #if MB_ROWS_SMEM == 6
 #define MB_FU_AT(i) u[(i) * MB_S_STRIDE]
+#if defined(MB_ROWS_P_SMEM) && MB_ROWS_P_SMEM > 0
+#define MB_FP_AT(i) p[(i) * MB_S_STRIDE]
+#endif
 #endif
 #include "generated/mbm_robot6dof.h"
 #ifndef MB_R_MINB

@@ -25,6 +25,12 @@
 #if !defined(MB_ROWS_NO_CARRY) && !defined(MB_ROWS_CARRY)
 #define MB_ROWS_CARRY        // carried stage accumulators (below); MB_ROWS_NO_CARRY selects the first formulation
 #endif
+#ifndef MB_ROWS_P_SMEM
+#define MB_ROWS_P_SMEM 0     // mode 6: number of parameters kept in shared memory (0 or NP; the model's MB_FP_AT must agree)
+#endif
+#ifndef MB_ROWS_LU_SMEM
+#define MB_ROWS_LU_SMEM 0
+#endif
 #ifndef MB_ROWS_JSPLIT
 #define MB_ROWS_JSPLIT 1     // slices of the component range in the stage-combination loop (must divide N)
 #endif
@@ -60,6 +66,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
   constexpr unsigned long long DTM = M::DT_MASK & (N >= 64 ? ~0ull : ((1ull << (N & 63)) - 1ull));
   constexpr int NDTS = SDT ? mb_popc64(DTM) : 0;
   constexpr int S_DT = N, S_US = N + NDTS, S_U = S_US + (SUS ? N : 0), S_LUS = S_U + (SU ? N : 0);
+  // mode 6 with MB_ROWS_P_SMEM = NP: the parameters too (read by every right-hand side, factor, dT and solve through MB_FP_AT)
+  constexpr bool SP = SU && MB_ROWS_P_SMEM > 0;
+  constexpr int S_P = S_LUS + MB_ROWS_LU_SMEM;
+  static_assert(!SP || (MB_ROWS_P_SMEM == M::NP && M::IS_ODE), "MB_ROWS_P_SMEM: NP slots, ODE models only (dae_init passes thread-local parameters)");
 #ifdef MB_ROWS_LUS0
   static_assert(MB_ROWS_LU_SMEM == 0 || S_LUS == MB_ROWS_LUS0, "MB_LU_AT of the model and the row layout disagree");
 #endif
@@ -116,6 +126,10 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
 #pragma unroll
           for (int i = 0; i < N; i++) MB_UU(i) = u[i];
         }
+        if (SP) {
+#pragma unroll
+          for (int i = 0; i < M::NP; i++) srow[(size_t)(S_P + i) * BLOCK] = p[i];
+        }
         active = true;
         if (!(t < a.t1)) rc = RC_SUCCESS;
         if (init_fail) rc = RC_INITIALFAILURE;
@@ -133,11 +147,12 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
       if (t + dt >= a.t1 - 100.0 * EPS * fabs(a.t1)) { dt = a.t1 - t; last = true; }
       const double cW = 1.0 / (dt * T::GAMMA);
       const double* const ust = SU ? srow + (size_t)S_U * BLOCK : u;      // the state as factor() / dT() address it
-      M::factor(ust, p, t, tb, cW, LU);
+      const double* const pst = SP ? srow + (size_t)S_P * BLOCK : p;      // the parameters as rhs_s() / factor() / dT() / solve() address them
+      M::factor(ust, pst, t, tb, cW, LU);
       const bool badpiv = !(M::pivmax(LU) <= MB_PIVOT_GUARD);     // statically ordered LU hit a numerically zero pivot
       njac++;
       if (M::HAS_DT) {
-        M::dT(ust, p, t, tb, dT);
+        M::dT(ust, pst, t, tb, dT);
         if (SDT) {
 #pragma unroll
           for (int i = 0; i < N; i++) if (MB_DTNZ(i)) srow[(size_t)MB_DTS(i) * BLOCK] = dT[i];
@@ -173,7 +188,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             if (SROWS) srow[(size_t)i * BLOCK] = y[i]; else sc[i] = y[i];
           }
           double r[N];
-          if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, r);
+          if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, pst, t + T::CT(s) * dt, tb, r);
           else M::rhs(us, p, t + T::CT(s) * dt, tb, r);
           const double dd = dt * T::D(s);
 #pragma unroll
@@ -183,7 +198,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             if (M::isdiff(i)) v = fma(SROWS ? srow[(size_t)i * BLOCK] : sc[i], inv_dt, v);
             r[i] = v;
           }
-          M::solve(LU, cW, p, r);
+          M::solve(LU, cW, SP ? pst : p, r);
 #pragma unroll
           for (int i = 0; i < N; i++) W[s][i] = r[i];
           {   // unconditional (the last stage writes values nobody reads): x, y must be dead across the right-hand side
@@ -239,7 +254,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
         // variant: the right-hand side hands its output over in registers instead of through the row k[s]
         {
           double r[N];
-          if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, r);
+          if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, pst, t + T::CT(s) * dt, tb, r);
           else M::rhs(us, p, t + T::CT(s) * dt, tb, r);
           const double dd = dt * T::D(s);
 #pragma unroll
@@ -250,7 +265,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             r[i] = v;
           }
 #else
-        if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, p, t + T::CT(s) * dt, tb, &W[s][0]);
+        if (SUS) M::rhs_s(srow + (size_t)S_US * BLOCK, pst, t + T::CT(s) * dt, tb, &W[s][0]);
         else M::rhs(us, p, t + T::CT(s) * dt, tb, &W[s][0]);     // du lands in the row that becomes k[s]
         {
           double r[N];
@@ -263,7 +278,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) rosenbrock_rows_kernel(const MbAr
             r[i] = v;
           }
 #endif
-          M::solve(LU, cW, p, r);
+          M::solve(LU, cW, SP ? pst : p, r);
 #pragma unroll
           for (int i = 0; i < N; i++) W[s][i] = r[i];
         }
