@@ -285,7 +285,9 @@ def rope(n_links: int = 6, name: str = "rope6") -> ReducedSystem:
     for c in range(3):
         mb.observed[f"body.r_0[{c+1}]"] = fr.r0[c].n      # rope end (what the docs animation shows)
     mech.solve_accelerations()
-    return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+    sysm = mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+    sysm.meta["strided_rhs"] = True        # rhs_s for the shared-memory rows of the Rosenbrock row kernel (csrc/mb_model_rope6.cu)
+    return sysm
 
 
 def rope_elastic(n_links: int = 3, name: str = "rope3e") -> ReducedSystem:
