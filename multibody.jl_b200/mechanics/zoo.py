@@ -324,7 +324,9 @@ def rope_elastic(n_links: int = 3, name: str = "rope3e") -> ReducedSystem:
     for k in range(3):
         mb.observed[f"body.r_0[{k+1}]"] = fr.r0[k].n
     mech.solve_accelerations()
-    return mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+    sysm = mb.finish(tspan=(0.0, 5.0), mechanism=mech)
+    sysm.meta["strided_rhs"] = True        # rhs_s for the shared-memory rows of the Rosenbrock row kernel
+    return sysm
 
 
 def fourbar_planar() -> ReducedSystem:
