@@ -114,3 +114,31 @@ def test_flop_counts_in_header_are_consistent():
     assert d["N"] == 36 and d["M"] == 19
     assert d["F_FACTOR"] >= d["F_JAC"] > d["F_RHS"] > 0
     assert d["F_SOLVE"] < 2 * 36 * 36          # structured solve beats the dense 2 n^2
+
+
+def test_df_dt_mask_and_strided_accessors_in_the_robot_header(oracle):
+    """The Rosenbrock row kernel keeps only the structurally non-zero rows of df/dt in shared memory
+    (MBM_*_DT_MASK, csrc/mb_rodas_rows.cuh) and reads state / parameters through MB_FU_AT / MB_FP_AT.  The mask must be
+    exactly the rows whose df/dt is not identically zero: 2 per axis (the controller rows the reference path enters)."""
+    import os
+    import re
+    here = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(here, "multibody.jl_b200", "csrc", "generated", "mbm_robot6dof.h")).read()
+    mask = int(re.search(r"#define MBM_robot6dof_DT_MASK 0x([0-9a-f]+)ull", text).group(1), 16)
+    assert bin(mask).count("1") == 12
+    body = text[text.index("void mbm_robot6dof_dT("):]
+    body = body[:body.index("\n}\n")]
+    zero_rows = {int(i) for i in re.findall(r"dT\[(\d+)\] = 0\.0;", body)}
+    assert zero_rows == {i for i in range(36) if not (mask >> i) & 1}
+    # numerically: finite-difference df/dt of the oracle's right-hand side vanishes exactly on the masked-out rows
+    from multibody_jl_b200 import ensembles
+    spec = ensembles.make_ensemble("C4", 1)
+    sysm = get_model("robot6dof")
+    u, p, tb = spec.u0[:, 0].copy(), spec.p[:, 0].copy(), sysm.tables.pack()
+    t, h = 0.37, 1e-6                                                        # inside the acceleration phase of the path
+    d = (oracle.eval_fn("robot6dof", 0, u, p, t + h, tb) - oracle.eval_fn("robot6dof", 0, u, p, t - h, tb)) / (2 * h)
+    assert all(d[i] == 0.0 for i in zero_rows) and all(d[i] != 0.0 for i in range(36) if (mask >> i) & 1)
+    for acc in ("MB_FU_AT(", "MB_FP_AT("):
+        assert acc in text[text.index("void mbm_robot6dof_factor("):]      # factor / solve read through the accessors
+    plain = text[text.index("void mbm_robot6dof_rhs("):text.index("#ifndef MB_FP_AT")]   # the plain rhs (initial step, Tsit5,
+    assert "MB_FP_AT(" not in plain and "p[" in plain                                   # observed) keeps thread-local parameters
